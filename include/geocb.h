@@ -1,0 +1,161 @@
+/* geocb.h -- C ABI of libgeocb.so: the sm_100a kernels behind the geodesic
+ * codebook builder (drop-in for m4rch1n0/vqvae `src/geo/*` + `build_codebook.py`).
+ *
+ * The reference has no FFI: its boundary is Python functions over host arrays
+ * (SURVEY.md §8b).  Each entry point below replaces the third-party CPU call a
+ * reference function makes; the reference call site is cited per function.
+ * INTEGRATION.md shows the ctypes stub a reference maintainer would add.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer unless its name ends in `_host`;
+ *  - `stream` is a cudaStream_t passed as void*; calls are stream-ordered and
+ *    do not synchronise unless stated ("syncs");
+ *  - return value: 0 = ok, otherwise a negative geocb code or a positive
+ *    cudaError_t; geocb_last_error() gives the text (thread-local);
+ *  - no CPU fallback exists: every function fails if no sm_100 device is usable.
+ */
+#ifndef GEOCB_H
+#define GEOCB_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GEOCB_ABI_VERSION 1
+#define GEOCB_ERR_ARG (-1)      /* bad argument */
+#define GEOCB_ERR_UNSUPPORTED (-2)
+#define GEOCB_ERR_WORKSPACE (-3) /* workspace too small */
+#define GEOCB_ERR_OVERFLOW (-4)
+
+int geocb_abi_version(void);
+const char* geocb_last_error(void);
+/* number of SMs, compute capability major*10+minor of the current device (syncs) */
+int geocb_device_info(int* sm_count, int* cc);
+
+/* ---------------------------------------------------------------- kNN ----
+ * replaces sklearn NearestNeighbors.fit/kneighbors (knn_graph_optimized.py:39-42).
+ * For query rows [q_lo,q_hi) of z[M,d] (row-major f32) find the kq nearest rows
+ * of z (self included), ordered by (exact fp64 squared distance, index).
+ *   pass 1: fused fp32 tiled  |b|^2 - 2ab  + per-thread top-(kq+slack) filter
+ *   pass 2: exact fp64 re-rank of the candidates; rows whose filter margin is
+ *           not provably safe are redone by an exact fp64 brute-force kernel.
+ * out_idx[(q_hi-q_lo),kq] int32, out_dist same shape f32 = sqrt(fp64 d2) (nullable).
+ * n_unsafe (device int32[1], nullable): rows that took the exact brute-force path. */
+int geocb_knn_topk(const float* z, int64_t M, int d, int64_t q_lo, int64_t q_hi, int kq,
+                   int32_t* out_idx, float* out_dist, int32_t* n_unsafe, void* stream);
+
+/* ------------------------------------------------- symmetrise -> CSR -----
+ * replaces scipy csr_matrix(...) ; W.maximum/minimum(W.T) ; setdiag(0) ;
+ * eliminate_zeros  (knn_graph_optimized.py:54-66).
+ * nbr_idx[M,k] (self already dropped), nbr_dist[M,k] or NULL (connectivity: data=1).
+ * mode: 0 = union (maximum), 1 = mutual (minimum).
+ * Two calls: _count fills indptr[M+1] (int64) and returns nnz in *nnz_host (syncs);
+ * _fill writes indices[nnz] (int32, ascending per row) and data[nnz] (f32). */
+int geocb_sym_count(const int32_t* nbr_idx, const float* nbr_dist, int64_t M, int k, int mode,
+                    int64_t* indptr, int64_t* nnz_host, void* stream);
+int geocb_sym_fill(const int32_t* nbr_idx, const float* nbr_dist, int64_t M, int k, int mode,
+                   const int64_t* indptr, int32_t* indices, float* data, void* stream);
+
+/* -------------------------------------------------- edge enumeration -----
+ * replaces W.nonzero(); keep rows<cols (build_codebook.py:43-45): upper-triangular
+ * entries in row-major order.  _count fills upper_ptr[M+1] (exclusive scan of the
+ * per-row count of cols>row) and returns E (syncs); _fill writes ei,ej[E] and the
+ * CSR positions of (i,j) and (j,i). */
+int geocb_upper_count(const int64_t* indptr, const int32_t* indices, int64_t M, int64_t* upper_ptr,
+                      int64_t* E_host, void* stream);
+int geocb_upper_fill(const int64_t* indptr, const int32_t* indices, int64_t M, const int64_t* upper_ptr,
+                     int32_t* ei, int32_t* ej, int64_t* pos_ij, int64_t* pos_ji, void* stream);
+
+/* ------------------------------------------- Riemannian edge reduce ------
+ * replaces vector_norm(dim=1) x2, 0.5*(a+b) (riemannian_metric.py:60-63) and the
+ * csr_matrix((L,(i,j))) + transpose of build_codebook.py:53-54.
+ * ja, jb [E,P] f32 = J(z_i)dz, J(z_j)dz for edges [e_lo, e_lo+E) ; writes
+ * len_out[e] (nullable) and data[pos_ij[e]] = data[pos_ji[e]] = L (pos nullable). */
+int geocb_edge_len_scatter(const float* ja, const float* jb, int64_t E, int P, int64_t e_lo,
+                           const int64_t* pos_ij, const int64_t* pos_ji, float* len_out, float* data,
+                           void* stream);
+
+/* --------------------------------------------- connected components ------
+ * replaces scipy.sparse.csgraph.connected_components (knn_graph_optimized.py:175).
+ * labels[n] = smallest vertex id of the component (undirected: the CSR must be
+ * structurally symmetric).  Syncs (iterates to a fixed point). */
+int geocb_cc_labels(const int64_t* indptr, const int32_t* indices, int64_t n, int32_t* labels, void* stream);
+/* largest component (ties -> smallest label, = np.argmax(np.bincount)); mask[n] u8,
+ * new_id[n] int32 (-1 outside); *n_keep_host, *n_comp_host returned (syncs). */
+int geocb_lcc_mask(const int32_t* labels, int64_t n, uint8_t* mask, int32_t* new_id, int64_t* n_keep_host,
+                   int64_t* n_comp_host, void* stream);
+/* W[mask][:,mask] for a union of whole components: rows copied, columns relabelled.
+ * out_indptr[n_keep+1] must be pre-sized; returns nnz_out in *nnz_host (syncs) from _count. */
+int geocb_csr_compact_count(const int64_t* indptr, const uint8_t* mask, const int32_t* new_id, int64_t n,
+                            int64_t* out_indptr, int64_t* nnz_host, void* stream);
+int geocb_csr_compact_fill(const int64_t* indptr, const int32_t* indices, const float* data, const uint8_t* mask,
+                           const int32_t* new_id, int64_t n, const int64_t* out_indptr, int32_t* out_indices,
+                           float* out_data, void* stream);
+
+/* ----------------------------------------------------------- SSSP --------
+ * Graph in "adjacency-pair" form: adj[row_ptr[v] .. row_ptr[v+1]) are 8-byte
+ * (int32 col, f32 weight) pairs; every row is padded to an even count so rows
+ * start 16-byte aligned (pad entries: col = v, weight = +inf).
+ * geocb_adj_count / _fill build it from CSR (unit_weights != 0 -> all weights 1,
+ * the reference's `unweighted=True`, geo_shortest_paths.py:31-33). */
+int geocb_adj_count(const int64_t* indptr, int64_t n, int64_t* row_ptr, int64_t* n_pairs_host, void* stream);
+int geocb_adj_fill(const int64_t* indptr, const int32_t* indices, const float* data, int64_t n, int unit_weights,
+                   const int64_t* row_ptr, void* adj, double* weight_sum /* device f64[1], nullable */, void* stream);
+
+/* workspace bytes for geocb_sssp_multi with `slots` concurrent sources */
+int64_t geocb_sssp_workspace_bytes(int64_t n, int slots);
+
+/* replaces scipy.sparse.csgraph.dijkstra(indices=sources) + astype(float32)
+ * (geo_shortest_paths.py:36-49).  S independent single-source problems solved by a
+ * near-far (delta-stepping) frontier relaxation that accumulates path sums in fp64
+ * exactly like scipy (monotone rounded addition => same fixed point as Dijkstra),
+ * `slots` sources in flight at once; results rounded to f32 at the end.
+ *   out_d32[S,n] f32 (+inf unreachable); out_pred[S,n] int32 or NULL
+ *   (predecessor = lowest-index neighbour u with fl(d[u]+w)==d[v]; -9999 for the
+ *   source and unreachable vertices, scipy's convention).
+ * delta <= 0 -> weight_mean (mean edge weight).  Syncs.  stats_host (nullable):
+ * int64[4] = {edge relaxations, rounds, threshold scans, improvements}. */
+int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t n, const int32_t* sources, int S,
+                     double delta, int slots, void* workspace, int64_t workspace_bytes, float* out_d32,
+                     int32_t* out_pred, int64_t* stats_host, void* stream);
+
+/* ------------------------------------------- incremental Voronoi SSSP ----
+ * The K-medoids path (kmeans_optimized.py:40-44, 97-100, 125-134) only ever uses
+ * d_min[v] = min_k D[k,v], argmin_k and sum d_min^2, so instead of K full SSSPs the
+ * state {dmin64, dmin32, label} is grown one centre at a time: inserting centre c
+ * with code k relaxes outwards from c and stops wherever the new distance is not
+ * smaller (exact in fp64 by monotonicity of rounded addition), then
+ *   dmin32[v] = f32(dmin64[v]);  label[v] = k  iff f32 value strictly decreased
+ * which is the reference's  argmin over k of float32(D[k,v]) with lowest-k ties.
+ * geocb_voronoi_init sets dmin64=+inf, dmin32=+inf, label=-1. */
+int64_t geocb_voronoi_workspace_bytes(int64_t n);
+int geocb_voronoi_init(int64_t n, double* dmin64, float* dmin32, int32_t* label, void* stream);
+int geocb_voronoi_insert(const int64_t* row_ptr, const void* adj, int64_t n, int32_t center, int32_t code,
+                         double delta, double* dmin64, float* dmin32, int32_t* label, void* workspace,
+                         int64_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------ k-means++ sampling -----
+ * replaces kmeans_optimized.py:47-61: inf handling, probs = d_min_safe**2,
+ * probs[centers]=0, probs.sum() (NumPy float32 pairwise tree, reproduced exactly),
+ * probs/=sum, and RandomState.choice's  cdf=cumsum(float64(p)); cdf/=cdf[-1];
+ * searchsorted(u,'right').  `u` is the MT19937 double drawn by the host.
+ * is_center[n] u8.  plan = device copy of the pairwise-sum plan built by
+ * geocb_pairwise_plan_host (host, int64 triples).  Returns in result_host[4] (syncs):
+ *   [0] chosen index (or -1 if probs.sum()==0 -> caller takes the reference's uniform fallback)
+ *   [1] 1 if the exact sequential-cumsum kernel had to be used, else 0
+ *   [2] float bits of probs.sum() before normalisation   [3] reserved */
+int64_t geocb_pairwise_plan_size(int64_t n);               /* number of int64 words */
+int geocb_pairwise_plan_host(int64_t n, int64_t* plan_host); /* host-side, no GPU needed */
+int64_t geocb_kpp_workspace_bytes(int64_t n);
+int geocb_kpp_draw(const float* dmin32, const uint8_t* is_center, int64_t n, double u, const int64_t* plan,
+                   void* workspace, int64_t workspace_bytes, int64_t* result_host, void* stream);
+/* float32 NumPy-pairwise sum of x[n] (exposed for tests and for QE) -> *out_host (syncs).
+ * square != 0: sums x*x (f32 multiply); only finite x are included when finite_only != 0,
+ * with the survivors compacted first exactly like d[finite_mask] (kmeans_optimized.py:129-132). */
+int geocb_pairwise_sum_f32(const float* x, int64_t n, int square, int finite_only, void* workspace,
+                           int64_t workspace_bytes, float* out_host, int64_t* n_used_host, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GEOCB_H */

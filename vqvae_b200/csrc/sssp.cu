@@ -1,0 +1,426 @@
+// sssp.cu -- multi-source / incremental-Voronoi shortest paths on the adjacency-pair graph.
+//
+// Replaces scipy.sparse.csgraph.dijkstra as called by the reference at
+// src/geo/geo_shortest_paths.py:36-49 (and through it kmeans_optimized.py:42,97,125).
+//
+// Algorithm: near-far (delta-stepping) frontier relaxation, push style.
+//   dist[v] is an fp64 kept as its uint64 bit pattern (non-negative doubles order as
+//   unsigned integers) so `atomicMin(u64)` is an exact fp64 min.  A relaxation computes
+//   fl64(dist[u] + (double)w) -- the same rounded addition, in the same source->target
+//   order, scipy's Dijkstra performs -- and because rounded addition is monotone the
+//   label-correcting fixed point is bit-identical to Dijkstra's result.
+//   One persistent cooperative kernel runs all rounds of `slots` concurrent sources:
+//     phase A  every queued (slot,u): 16 lanes stream u's (col,w) pairs with 128-bit loads,
+//              gather dist[v] from L2, atomicMin the improvements and queue v
+//              (near: cand < thr[slot]) or mark it dirty (far);
+//     phase B  for slots whose near queue ran dry: thr = min(dirty dist)+delta, queue dirty<thr.
+// HBM model: 8 B per relaxation streamed (the pair) + 8 B dist gather (L2 resident
+// when slots*n*8 B fits) ; algorithmic bytes = 16*(nnz+n) per source.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kMaxSlots = 32;
+constexpr int kThreads = 256;
+constexpr int kGroup = 16;  // lanes cooperating on one vertex (16 x uint4 = 32 pairs per step)
+
+struct SlotCtl {
+    double thr;                  // current near/far threshold
+    unsigned long long far_min;  // min dist bits over dirty vertices (phase B1)
+    int cnt[3];                  // queue sizes, rotating: round r reads cnt[r%3], fills cnt[(r+1)%3], clears cnt[(r+2)%3]
+    int done;
+    int pad[2];
+};
+
+struct SsspParams {
+    const int64_t* row_ptr;
+    const uint4* adj4;
+    int64_t n;
+    int nslots;
+    double delta;
+    unsigned long long* dist;  // [nslots][n]
+    int* state;                // [nslots][n]  0 clean, 1 dirty (far), 2 queued (near)
+    uint32_t* queue[2];        // [nslots][n] each
+    SlotCtl* ctl;              // [nslots]
+    unsigned long long* stats; // [4]
+    // full-SSSP mode
+    const int32_t* sources;  // [nslots]
+    float* out_d32;          // [nslots][n]
+    int32_t* out_pred;       // nullable
+    // voronoi mode
+    int voronoi;
+    int32_t center, code;
+    float* dmin32;
+    int32_t* label;
+};
+
+__device__ __forceinline__ void relax_pair(uint32_t v, uint32_t wbits, double du, unsigned long long* dist_s,
+                                           int* state_s, double thr, uint32_t* qnext, int* cnt_next,
+                                           unsigned& n_improve) {
+    double cand = du + (double)__uint_as_float(wbits);
+    unsigned long long cb = (unsigned long long)__double_as_longlong(cand);
+    unsigned long long cur = ld_cg_u64(dist_s + v);
+    if (cb < cur) {
+        unsigned long long old = atomicMin(dist_s + v, cb);
+        if (cb < old) {
+            ++n_improve;
+            if (cand < thr) {
+                if (atomicExch(state_s + v, 2) != 2) {
+                    int pos = atomicAdd(cnt_next, 1);
+                    qnext[pos] = v;
+                }
+            } else {
+                atomicMax(state_s + v, 1);
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
+    cg::grid_group grid = cg::this_grid();
+    const int64_t n = p.n;
+    const int B = p.nslots;
+    const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
+    __shared__ int s_cnt[kMaxSlots + 1];
+    __shared__ int s_flag, s_alldone;
+    __shared__ unsigned long long s_red[kThreads / 32];
+
+    // ---- init ----
+    if (!p.voronoi) {
+        for (int64_t i = gtid; i < (int64_t)B * n; i += gthreads) {
+            p.dist[i] = D64_INF_BITS;
+            p.state[i] = 0;
+        }
+    }
+    grid.sync();
+    if (gtid < B) {
+        int s = (int)gtid;
+        int src = p.voronoi ? p.center : p.sources[s];
+        SlotCtl c;
+        c.thr = p.delta;
+        c.far_min = D64_INF_BITS;
+        c.cnt[0] = 0;
+        c.cnt[1] = 0;
+        c.cnt[2] = 0;
+        c.done = 0;
+        unsigned long long old = atomicMin(p.dist + (int64_t)s * n + src, 0ULL);
+        if (old != 0ULL) {  // (voronoi: re-inserting an existing centre changes nothing)
+            p.state[(int64_t)s * n + src] = 2;
+            p.queue[0][(int64_t)s * n] = (uint32_t)src;
+            c.cnt[0] = 1;
+        }
+        p.ctl[s] = c;
+    }
+    grid.sync();
+
+    unsigned n_relax = 0, n_improve = 0, n_rounds = 0, n_scans = 0;
+    const int lane = threadIdx.x & (kGroup - 1);
+    const int64_t ggroup = gtid / kGroup;
+    const int64_t ngroups = gthreads / kGroup;
+
+    for (int round = 0;; ++round) {
+        const int par = round & 1;            // queue buffer parity
+        const int c_cur = round % 3, c_next = (round + 1) % 3, c_clear = (round + 2) % 3;
+        if (gtid < B) {  // safe: both were last touched before the previous grid.sync
+            p.ctl[gtid].cnt[c_clear] = 0;
+            p.ctl[gtid].far_min = D64_INF_BITS;
+        }
+        // ---- phase A: relax every queued vertex ----
+        if (threadIdx.x <= B) {
+            int acc = 0;
+            for (int s = 0; s < (int)threadIdx.x; ++s) acc += ld_cg_s32(&p.ctl[s].cnt[c_cur]);
+            s_cnt[threadIdx.x] = acc;  // exclusive prefix; s_cnt[B] = total
+        }
+        __syncthreads();
+        const int total = s_cnt[B];
+        for (int64_t item = ggroup; item < total; item += ngroups) {
+            int s = 0;
+            while (s + 1 < B && item >= s_cnt[s + 1]) ++s;
+            const int64_t base = (int64_t)s * n;
+            unsigned long long* dist_s = p.dist + base;
+            int* state_s = p.state + base;
+            const uint32_t u = p.queue[par][base + (item - s_cnt[s])];
+            double du = 0.0;
+            if (lane == 0) {
+                atomicExch(state_s + u, 0);
+                __threadfence();
+                du = __longlong_as_double((long long)ld_cg_u64(dist_s + u));
+            }
+            du = __shfl_sync(0xffffffffu, du, 0, kGroup);
+            const double thr = __longlong_as_double((long long)ld_cg_u64((const unsigned long long*)&p.ctl[s].thr));
+            const int64_t beg = p.row_ptr[u] >> 1, end = p.row_ptr[u + 1] >> 1;
+            uint32_t* qnext = p.queue[par ^ 1] + base;
+            int* cnt_next = &p.ctl[s].cnt[c_next];
+            for (int64_t i = beg + lane; i < end; i += kGroup) {
+                uint4 e = ld_stream_v4(p.adj4 + i);
+                n_relax += 2;
+                relax_pair(e.x, e.y, du, dist_s, state_s, thr, qnext, cnt_next, n_improve);
+                relax_pair(e.z, e.w, du, dist_s, state_s, thr, qnext, cnt_next, n_improve);
+            }
+        }
+        grid.sync();
+        ++n_rounds;
+        // ---- control: which slots ran dry? (uniform across the grid) ----
+        if (threadIdx.x == 0) s_flag = 0;
+        __syncthreads();
+        if (threadIdx.x < B) {
+            int s = threadIdx.x;
+            int need = (!ld_cg_s32(&p.ctl[s].done)) && ld_cg_s32(&p.ctl[s].cnt[c_next]) == 0;
+            s_cnt[s] = need;
+            if (need) s_flag = 1;
+        }
+        __syncthreads();
+        const int any_scan = s_flag;
+        if (any_scan) {
+            ++n_scans;
+            // ---- phase B1: min dist over dirty vertices of each dry slot ----
+            for (int s = 0; s < B; ++s) {
+                if (!s_cnt[s]) continue;
+                const int64_t base = (int64_t)s * n;
+                unsigned long long m = D64_INF_BITS;
+                for (int64_t v = gtid; v < n; v += gthreads)
+                    if (ld_cg_s32(p.state + base + v) == 1) {
+                        unsigned long long d = ld_cg_u64(p.dist + base + v);
+                        m = d < m ? d : m;
+                    }
+                for (int o = 16; o; o >>= 1) {
+                    unsigned long long t = __shfl_xor_sync(0xffffffffu, m, o);
+                    m = t < m ? t : m;
+                }
+                if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = m;
+                __syncthreads();
+                if (threadIdx.x == 0) {
+                    for (int w = 1; w < kThreads / 32; ++w) m = s_red[w] < m ? s_red[w] : m;
+                    if (m != D64_INF_BITS) atomicMin(&p.ctl[s].far_min, m);
+                }
+                __syncthreads();
+            }
+            grid.sync();
+            // ---- phase B2: raise thr, queue dirty vertices below it ----
+            for (int s = 0; s < B; ++s) {
+                if (!s_cnt[s]) continue;
+                const unsigned long long fm = ld_cg_u64(&p.ctl[s].far_min);
+                if (fm == D64_INF_BITS) {  // nothing dirty: this source has converged
+                    if (gtid == 0) p.ctl[s].done = 1;
+                    continue;
+                }
+                const double thr_new = __longlong_as_double((long long)fm) + p.delta;
+                const int64_t base = (int64_t)s * n;
+                uint32_t* qnext = p.queue[par ^ 1] + base;
+                for (int64_t v = gtid; v < n; v += gthreads)
+                    if (ld_cg_s32(p.state + base + v) == 1) {
+                        double d = __longlong_as_double((long long)ld_cg_u64(p.dist + base + v));
+                        if (d < thr_new) {
+                            p.state[base + v] = 2;
+                            int pos = atomicAdd(&p.ctl[s].cnt[c_next], 1);
+                            qnext[pos] = (uint32_t)v;
+                        }
+                    }
+                if (gtid == 0) p.ctl[s].thr = thr_new;
+            }
+            grid.sync();
+        }
+        // ---- termination test (uniform: `done` only changes in B2, which ends with a grid.sync) ----
+        if (threadIdx.x == 0) s_alldone = 1;
+        __syncthreads();
+        if (threadIdx.x < B && !ld_cg_s32(&p.ctl[threadIdx.x].done)) s_alldone = 0;
+        __syncthreads();
+        if (s_alldone) break;
+    }
+
+    // ---- finalize ----
+    if (p.voronoi) {
+        // dmin32 = f32(dmin64); label = code iff the f32 value strictly decreased
+        // (reference: argmin over k of float32(D[k,v]), lowest k on ties, kmeans_optimized.py:100)
+        for (int64_t v = gtid; v < n; v += gthreads) {
+            float nd = __double2float_rn(__longlong_as_double((long long)p.dist[v]));
+            if (nd < p.dmin32[v]) {
+                p.dmin32[v] = nd;
+                p.label[v] = p.code;
+            }
+        }
+    } else {
+        for (int64_t i = gtid; i < (int64_t)B * n; i += gthreads)
+            p.out_d32[i] = __double2float_rn(__longlong_as_double((long long)p.dist[i]));
+        if (p.out_pred) {
+            for (int64_t item = ggroup; item < (int64_t)B * n; item += ngroups) {
+                const int s = (int)(item / n);
+                const int64_t v = item - (int64_t)s * n;
+                const unsigned long long* dist_s = p.dist + (int64_t)s * n;
+                const unsigned long long dv = dist_s[v];
+                int best = 0x7fffffff;
+                if (dv != D64_INF_BITS && v != p.sources[s]) {
+                    const int64_t beg = p.row_ptr[v] >> 1, end = p.row_ptr[v + 1] >> 1;
+                    for (int64_t i = beg + lane; i < end; i += kGroup) {
+                        uint4 e = ld_stream_v4(p.adj4 + i);
+                        double c0 = __longlong_as_double((long long)dist_s[e.x]) + (double)__uint_as_float(e.y);
+                        double c1 = __longlong_as_double((long long)dist_s[e.z]) + (double)__uint_as_float(e.w);
+                        if ((unsigned long long)__double_as_longlong(c0) == dv && (int)e.x < best) best = (int)e.x;
+                        if ((unsigned long long)__double_as_longlong(c1) == dv && (int)e.z < best) best = (int)e.z;
+                    }
+                }
+                for (int o = kGroup / 2; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o, kGroup));
+                if (lane == 0) p.out_pred[item] = best == 0x7fffffff ? -9999 : best;
+            }
+        }
+    }
+    if (p.stats) {
+        for (int o = 16; o; o >>= 1) {
+            n_relax += __shfl_xor_sync(0xffffffffu, n_relax, o);
+            n_improve += __shfl_xor_sync(0xffffffffu, n_improve, o);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(p.stats + 0, (unsigned long long)n_relax);
+            atomicAdd(p.stats + 3, (unsigned long long)n_improve);
+        }
+        if (gtid == 0) {
+            atomicAdd(p.stats + 1, (unsigned long long)n_rounds);
+            atomicAdd(p.stats + 2, (unsigned long long)n_scans);
+        }
+    }
+}
+
+int coop_grid(int* grid_out) {
+    DevInfo di;
+    int rc = geocb_devinfo(&di);
+    if (rc) return rc;
+    int occ = 0;
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sssp_kernel, kThreads, 0));
+    if (occ < 1) {
+        geocb_set_error("sssp_kernel cannot be resident (occupancy 0)");
+        return GEOCB_ERR_UNSUPPORTED;
+    }
+    *grid_out = di.sm_count * occ;
+    return 0;
+}
+
+struct WsLayout {
+    int64_t dist, state, q0, q1, ctl, stats, total;
+};
+WsLayout ws_layout(int64_t n, int slots, bool own_dist) {
+    WsLayout w;
+    int64_t off = 0;
+    w.dist = off;
+    if (own_dist) off += align_up((int64_t)slots * n * 8, 256);
+    w.state = off;
+    off += align_up((int64_t)slots * n * 4, 256);
+    w.q0 = off;
+    off += align_up((int64_t)slots * n * 4, 256);
+    w.q1 = off;
+    off += align_up((int64_t)slots * n * 4, 256);
+    w.ctl = off;
+    off += align_up((int64_t)kMaxSlots * sizeof(SlotCtl), 256);
+    w.stats = off;
+    off += 256;
+    w.total = off;
+    return w;
+}
+
+}  // namespace
+
+GEOCB_API int64_t geocb_sssp_workspace_bytes(int64_t n, int slots) {
+    if (n < 0 || slots < 1 || slots > kMaxSlots) return -1;
+    return ws_layout(n, slots, true).total;
+}
+
+GEOCB_API int64_t geocb_voronoi_workspace_bytes(int64_t n) {
+    if (n < 0) return -1;
+    return ws_layout(n, 1, false).total;
+}
+
+GEOCB_API int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t n, const int32_t* sources, int S,
+                               double delta, int slots, void* workspace, int64_t workspace_bytes, float* out_d32,
+                               int32_t* out_pred, int64_t* stats_host, void* stream) {
+    ARG_CHECK(row_ptr && adj && sources && out_d32 && workspace);
+    ARG_CHECK(n > 0 && n < (1LL << 31) && S > 0 && slots >= 1 && slots <= kMaxSlots && delta > 0);
+    WsLayout w = ws_layout(n, slots, true);
+    if (workspace_bytes < w.total) {
+        geocb_set_error("sssp workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)w.total);
+        return GEOCB_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    char* ws = (char*)workspace;
+    int grid = 0;
+    int rc = coop_grid(&grid);
+    if (rc) return rc;
+    CU_TRY(cudaMemsetAsync(ws + w.stats, 0, 32, st));
+    for (int s0 = 0; s0 < S; s0 += slots) {
+        SsspParams p;
+        memset(&p, 0, sizeof(p));
+        p.row_ptr = row_ptr;
+        p.adj4 = (const uint4*)adj;
+        p.n = n;
+        p.nslots = (S - s0) < slots ? (S - s0) : slots;
+        p.delta = delta;
+        p.dist = (unsigned long long*)(ws + w.dist);
+        p.state = (int*)(ws + w.state);
+        p.queue[0] = (uint32_t*)(ws + w.q0);
+        p.queue[1] = (uint32_t*)(ws + w.q1);
+        p.ctl = (SlotCtl*)(ws + w.ctl);
+        p.stats = (unsigned long long*)(ws + w.stats);
+        p.sources = sources + s0;
+        p.out_d32 = out_d32 + (int64_t)s0 * n;
+        p.out_pred = out_pred ? out_pred + (int64_t)s0 * n : nullptr;
+        p.voronoi = 0;
+        void* args[] = {&p};
+        CU_TRY(cudaLaunchCooperativeKernel((void*)sssp_kernel, dim3(grid), dim3(kThreads), args, 0, st));
+    }
+    if (stats_host) CU_TRY(cudaMemcpyAsync(stats_host, ws + w.stats, 32, cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    return 0;
+}
+
+namespace {
+__global__ void voronoi_init_kernel(int64_t n, unsigned long long* d64, float* d32, int32_t* label) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        d64[i] = D64_INF_BITS;
+        d32[i] = __uint_as_float(F32_INF_BITS);
+        label[i] = -1;
+    }
+}
+}  // namespace
+
+GEOCB_API int geocb_voronoi_init(int64_t n, double* dmin64, float* dmin32, int32_t* label, void* stream) {
+    ARG_CHECK(n > 0 && dmin64 && dmin32 && label);
+    voronoi_init_kernel<<<592, 256, 0, (cudaStream_t)stream>>>(n, (unsigned long long*)dmin64, dmin32, label);
+    KERNEL_CHECK();
+    return 0;
+}
+
+GEOCB_API int geocb_voronoi_insert(const int64_t* row_ptr, const void* adj, int64_t n, int32_t center, int32_t code,
+                                   double delta, double* dmin64, float* dmin32, int32_t* label, void* workspace,
+                                   int64_t workspace_bytes, void* stream) {
+    ARG_CHECK(row_ptr && adj && dmin64 && dmin32 && label && workspace);
+    ARG_CHECK(n > 0 && n < (1LL << 31) && center >= 0 && center < n && delta > 0);
+    WsLayout w = ws_layout(n, 1, false);
+    if (workspace_bytes < w.total) {
+        geocb_set_error("voronoi workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)w.total);
+        return GEOCB_ERR_WORKSPACE;
+    }
+    char* ws = (char*)workspace;
+    int grid = 0;
+    int rc = coop_grid(&grid);
+    if (rc) return rc;
+    SsspParams p;
+    memset(&p, 0, sizeof(p));
+    p.row_ptr = row_ptr;
+    p.adj4 = (const uint4*)adj;
+    p.n = n;
+    p.nslots = 1;
+    p.delta = delta;
+    p.dist = (unsigned long long*)dmin64;
+    p.state = (int*)(ws + w.state);  // must be all-zero on entry; the kernel leaves it all-zero
+    p.queue[0] = (uint32_t*)(ws + w.q0);
+    p.queue[1] = (uint32_t*)(ws + w.q1);
+    p.ctl = (SlotCtl*)(ws + w.ctl);
+    p.stats = nullptr;
+    p.voronoi = 1;
+    p.center = center;
+    p.code = code;
+    p.dmin32 = dmin32;
+    p.label = label;
+    void* args[] = {&p};
+    CU_TRY(cudaLaunchCooperativeKernel((void*)sssp_kernel, dim3(grid), dim3(kThreads), args, 0, (cudaStream_t)stream));
+    return 0;
+}

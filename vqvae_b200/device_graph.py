@@ -1,0 +1,257 @@
+"""Device-resident graph objects and thin wrappers over the C ABI (include/geocb.h).
+
+Everything here works on torch CUDA tensors; the reference-facing modules in
+`vqvae_b200.geo` convert host arrays <-> these objects at the API boundary.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import check, ptr, stream_ptr
+
+
+def _i64():
+    return C.c_int64(0)
+
+
+class DeviceCSR:
+    """CSR matrix in HBM: indptr int64[n+1], indices int32[nnz] (ascending per row), data f32[nnz]."""
+
+    def __init__(self, indptr, indices, data, n):
+        self.indptr, self.indices, self.data, self.n = indptr, indices, data, int(n)
+        self._adj = {}
+
+    @property
+    def nnz(self):
+        return int(self.indices.numel())
+
+    @classmethod
+    def from_scipy(cls, W, device):
+        W = W.tocsr()
+        if not W.has_sorted_indices:
+            W = W.sorted_indices()
+        return cls(torch.from_numpy(W.indptr.astype(np.int64)).to(device),
+                   torch.from_numpy(W.indices.astype(np.int32)).to(device),
+                   torch.from_numpy(W.data.astype(np.float32)).to(device), W.shape[0])
+
+    def to_scipy(self):
+        from scipy import sparse
+        ip = self.indptr.cpu().numpy()
+        ip = ip.astype(np.int32) if self.nnz < 2**31 - 1 else ip
+        return sparse.csr_matrix((self.data.cpu().numpy(), self.indices.cpu().numpy(), ip), shape=(self.n, self.n))
+
+    # -- adjacency-pair form used by the SSSP kernels (rows padded to even length, 16 B aligned) --
+    def adjacency(self, unit_weights=False):
+        key = bool(unit_weights)
+        if key not in self._adj:
+            lib = _lib.load()
+            dev = self.indptr.device
+            row_ptr = torch.empty(self.n + 1, dtype=torch.int64, device=dev)
+            npairs = _i64()
+            check(lib.geocb_adj_count(ptr(self.indptr), self.n, ptr(row_ptr), C.byref(npairs), stream_ptr()), "adj_count")
+            adj = torch.empty(max(npairs.value, 2), dtype=torch.int64, device=dev)  # 8-byte (col,w) pairs
+            wsum = torch.zeros(1, dtype=torch.float64, device=dev)
+            check(lib.geocb_adj_fill(ptr(self.indptr), ptr(self.indices), ptr(self.data), self.n, int(unit_weights),
+                                     ptr(row_ptr), ptr(adj), ptr(wsum), stream_ptr()), "adj_fill")
+            mean_w = float(wsum.item()) / max(self.nnz, 1)
+            self._adj[key] = (row_ptr, adj, mean_w)
+        return self._adj[key]
+
+
+# --------------------------------------------------------------------------- kNN
+def knn_topk(z, kq, q_lo=0, q_hi=None, want_dist=True):
+    """kq nearest rows of z (self included) for query rows [q_lo,q_hi): (idx int32, dist f32|None, n_exact_rows)."""
+    lib = _lib.load()
+    assert z.is_cuda and z.dtype == torch.float32 and z.is_contiguous()
+    M, d = z.shape
+    q_hi = M if q_hi is None else q_hi
+    nq = q_hi - q_lo
+    idx = torch.empty((nq, kq), dtype=torch.int32, device=z.device)
+    dist = torch.empty((nq, kq), dtype=torch.float32, device=z.device) if want_dist else None
+    nun = torch.zeros(1, dtype=torch.int32, device=z.device)
+    check(lib.geocb_knn_topk(ptr(z), M, d, q_lo, q_hi, kq, ptr(idx), ptr(dist), ptr(nun), stream_ptr()), "knn_topk")
+    return idx, dist, nun
+
+
+def symmetrize(nbr_idx, nbr_dist, mode):
+    """kNN lists (self dropped) -> symmetric DeviceCSR.  mode 'union' | 'mutual'; nbr_dist None => weights 1."""
+    lib = _lib.load()
+    M, k = nbr_idx.shape
+    dev = nbr_idx.device
+    m = {"union": 0, "mutual": 1}[mode]
+    indptr = torch.empty(M + 1, dtype=torch.int64, device=dev)
+    nnz = _i64()
+    check(lib.geocb_sym_count(ptr(nbr_idx), ptr(nbr_dist), M, k, m, ptr(indptr), C.byref(nnz), stream_ptr()), "sym_count")
+    indices = torch.empty(nnz.value, dtype=torch.int32, device=dev)
+    data = torch.empty(nnz.value, dtype=torch.float32, device=dev)
+    if nnz.value:
+        check(lib.geocb_sym_fill(ptr(nbr_idx), ptr(nbr_dist), M, k, m, ptr(indptr), ptr(indices), ptr(data),
+                                 stream_ptr()), "sym_fill")
+    return DeviceCSR(indptr, indices, data, M)
+
+
+def upper_edges(g: DeviceCSR):
+    """Upper-triangular entries in row-major order: (ei, ej int32[E], pos_ij, pos_ji int64[E])."""
+    lib = _lib.load()
+    dev = g.indptr.device
+    up = torch.empty(g.n + 1, dtype=torch.int64, device=dev)
+    E = _i64()
+    check(lib.geocb_upper_count(ptr(g.indptr), ptr(g.indices), g.n, ptr(up), C.byref(E), stream_ptr()), "upper_count")
+    ei = torch.empty(E.value, dtype=torch.int32, device=dev)
+    ej = torch.empty(E.value, dtype=torch.int32, device=dev)
+    pij = torch.empty(E.value, dtype=torch.int64, device=dev)
+    pji = torch.empty(E.value, dtype=torch.int64, device=dev)
+    if E.value:
+        check(lib.geocb_upper_fill(ptr(g.indptr), ptr(g.indices), g.n, ptr(up), ptr(ei), ptr(ej), ptr(pij), ptr(pji),
+                                   stream_ptr()), "upper_fill")
+    return ei, ej, pij, pji
+
+
+def edge_len_scatter(ja, jb, e_lo, pos_ij, pos_ji, len_out, data):
+    lib = _lib.load()
+    E, P = ja.shape
+    check(lib.geocb_edge_len_scatter(ptr(ja), ptr(jb), E, P, e_lo, ptr(pos_ij), ptr(pos_ji), ptr(len_out), ptr(data),
+                                     stream_ptr()), "edge_len_scatter")
+
+
+# ------------------------------------------------------------ components / LCC
+def component_labels(g: DeviceCSR):
+    lib = _lib.load()
+    labels = torch.empty(g.n, dtype=torch.int32, device=g.indptr.device)
+    check(lib.geocb_cc_labels(ptr(g.indptr), ptr(g.indices), g.n, ptr(labels), stream_ptr()), "cc_labels")
+    return labels
+
+
+def largest_component(g: DeviceCSR):
+    """(mask uint8[n], new_id int32[n], n_keep, n_components)."""
+    lib = _lib.load()
+    labels = component_labels(g)
+    dev = g.indptr.device
+    mask = torch.empty(g.n, dtype=torch.uint8, device=dev)
+    new_id = torch.empty(g.n, dtype=torch.int32, device=dev)
+    nk, nc = _i64(), _i64()
+    check(lib.geocb_lcc_mask(ptr(labels), g.n, ptr(mask), ptr(new_id), C.byref(nk), C.byref(nc), stream_ptr()), "lcc_mask")
+    return mask, new_id, nk.value, nc.value
+
+
+def compact(g: DeviceCSR, mask, new_id, n_keep):
+    """W[mask][:,mask] where mask is a union of whole components."""
+    lib = _lib.load()
+    dev = g.indptr.device
+    out_ptr = torch.empty(n_keep + 1, dtype=torch.int64, device=dev)
+    nnz = _i64()
+    check(lib.geocb_csr_compact_count(ptr(g.indptr), ptr(mask), ptr(new_id), g.n, ptr(out_ptr), C.byref(nnz),
+                                      stream_ptr()), "csr_compact_count")
+    oi = torch.empty(nnz.value, dtype=torch.int32, device=dev)
+    od = torch.empty(nnz.value, dtype=torch.float32, device=dev)
+    if nnz.value:
+        check(lib.geocb_csr_compact_fill(ptr(g.indptr), ptr(g.indices), ptr(g.data), ptr(mask), ptr(new_id), g.n,
+                                         ptr(out_ptr), ptr(oi), ptr(od), stream_ptr()), "csr_compact_fill")
+    return DeviceCSR(out_ptr, oi, od, n_keep)
+
+
+# ------------------------------------------------------------------------ SSSP
+_ws_cache = {}
+
+
+def _workspace(tag, nbytes, device, zero=False):
+    key = (tag, device)
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+        _ws_cache[key] = buf
+    elif zero:
+        buf.zero_()
+    return buf
+
+
+def default_slots(n):
+    """Concurrent sources per launch: keep slots*n*8 B of fp64 distances inside ~96 MB of L2."""
+    return int(max(1, min(16, (96 << 20) // max(1, n * 8))))
+
+
+def sssp_multi(g: DeviceCSR, sources, unweighted=False, want_pred=False, delta=None, slots=None, out=None,
+               stats=False):
+    """S independent SSSPs -> D32[S,n] (+pred int32[S,n]) on the device."""
+    lib = _lib.load()
+    dev = g.indptr.device
+    row_ptr, adj, mean_w = g.adjacency(unweighted)
+    src = torch.as_tensor(np.asarray(sources, dtype=np.int32), device=dev)
+    S = int(src.numel())
+    if delta is None:
+        delta = mean_w if mean_w > 0 else 1.0
+    slots = default_slots(g.n) if slots is None else slots
+    slots = max(1, min(slots, S, 32))
+    nbytes = lib.geocb_sssp_workspace_bytes(g.n, slots)
+    ws = _workspace("sssp", nbytes, dev)
+    D = out if out is not None else torch.empty((S, g.n), dtype=torch.float32, device=dev)
+    P = torch.empty((S, g.n), dtype=torch.int32, device=dev) if want_pred else None
+    st = (C.c_int64 * 4)()
+    check(lib.geocb_sssp_multi(ptr(row_ptr), ptr(adj), g.n, ptr(src), S, float(delta), slots, ptr(ws), ws.numel(),
+                               ptr(D), ptr(P), st, stream_ptr()), "sssp_multi")
+    res = (D, P) if want_pred else D
+    if stats:
+        return res, dict(relaxations=st[0], rounds=st[1], scans=st[2], improvements=st[3], slots=slots, delta=delta)
+    return res
+
+
+class VoronoiState:
+    """Running (dmin64, dmin32, label) over the inserted centres -- see geocb_voronoi_insert."""
+
+    def __init__(self, g: DeviceCSR, unweighted=False):
+        lib = _lib.load()
+        self.g = g
+        dev = g.indptr.device
+        self.row_ptr, self.adj, self.mean_w = g.adjacency(unweighted)
+        n = g.n
+        self.dmin64 = torch.empty(n, dtype=torch.float64, device=dev)
+        self.dmin32 = torch.empty(n, dtype=torch.float32, device=dev)
+        self.label = torch.empty(n, dtype=torch.int32, device=dev)
+        self.is_center = torch.zeros(n, dtype=torch.uint8, device=dev)
+        self.ws = torch.zeros(lib.geocb_voronoi_workspace_bytes(n), dtype=torch.uint8, device=dev)
+        self.kpp_ws = None
+        self.plan = None
+        self.count = 0
+        check(lib.geocb_voronoi_init(n, ptr(self.dmin64), ptr(self.dmin32), ptr(self.label), stream_ptr()), "voronoi_init")
+
+    def insert(self, center, code=None):
+        lib = _lib.load()
+        code = self.count if code is None else code
+        # near-far only pays off while cells are large; later cells are tiny -> plain frontier relaxation
+        delta = self.mean_w if (self.count < 8 and self.mean_w > 0) else float("inf")
+        check(lib.geocb_voronoi_insert(ptr(self.row_ptr), ptr(self.adj), self.g.n, int(center), int(code), delta,
+                                       ptr(self.dmin64), ptr(self.dmin32), ptr(self.label), ptr(self.ws),
+                                       self.ws.numel(), stream_ptr()), "voronoi_insert")
+        self.is_center[int(center)] = 1
+        self.count += 1
+
+    def draw(self, u):
+        """One k-means++ draw with the host's MT19937 double u -> (index or -1, used_exact_path, probs_sum)."""
+        lib = _lib.load()
+        n = self.g.n
+        dev = self.dmin32.device
+        if self.plan is None:
+            words = lib.geocb_pairwise_plan_size(n)
+            host = (C.c_int64 * words)()
+            check(lib.geocb_pairwise_plan_host(n, host), "pairwise_plan_host")
+            self.plan = torch.from_numpy(np.frombuffer(host, dtype=np.int64).copy()).to(dev)
+            self.kpp_ws = torch.empty(lib.geocb_kpp_workspace_bytes(n), dtype=torch.uint8, device=dev)
+        res = (C.c_int64 * 4)()
+        check(lib.geocb_kpp_draw(ptr(self.dmin32), ptr(self.is_center), n, float(u), ptr(self.plan), ptr(self.kpp_ws),
+                                 self.kpp_ws.numel(), res, stream_ptr()), "kpp_draw")
+        psum = np.array([res[2]], dtype=np.uint32).view(np.float32)[0]
+        return int(res[0]), int(res[1]), float(psum)
+
+
+def pairwise_sum_f32(x, square=False, finite_only=False):
+    """NumPy-exact float32 np.sum(x) / np.sum(x[isfinite]**2) -> (float32 value, n_used)."""
+    lib = _lib.load()
+    out = C.c_float(0.0)
+    used = _i64()
+    check(lib.geocb_pairwise_sum_f32(ptr(x), x.numel(), int(square), int(finite_only), None, 0, C.byref(out),
+                                     C.byref(used), stream_ptr()), "pairwise_sum_f32")
+    return np.float32(out.value), used.value

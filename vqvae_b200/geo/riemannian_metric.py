@@ -1,0 +1,222 @@
+"""Riemannian (decoder pull-back) edge lengths -- drop-in for the reference's
+`src/geo/riemannian_metric.py` (citations are lines of that file).
+
+    L(i,j) = 0.5 * ( |J(z_i) dz| + |J(z_j) dz| ),   J = Jacobian of sigmoid(decoder(z)),  dz = z_j - z_i
+
+The JVPs stay in PyTorch (north star): conv/BN/ReLU stacks are propagated in explicit
+forward mode (primal and tangent share one convolution call) with BatchNorm statistics
+taken per `batch_size`-edge batch exactly as the reference's loop does (:50-58) -- the
+reference CLI leaves the decoder in train mode (build_codebook.py:27-29), so results
+depend on batch membership.  Many batches are processed per call by grouping the BN
+statistics.  The per-edge reduction + scatter into both CSR directions is the CUDA
+kernel `geocb_edge_len_scatter`.  Unknown module types fall back to
+`torch.autograd.functional.jvp` per batch (still on the GPU).
+"""
+from __future__ import annotations
+
+import contextlib
+import copy
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .. import _lib
+from .. import device_graph as dg
+
+
+@torch.no_grad()
+def decoder_logits_to_img(logits: torch.Tensor) -> torch.Tensor:
+    """Convert decoder logits to image space [0,1] using sigmoid (:7-10)."""
+    return torch.sigmoid(logits)
+
+
+def _is_flat_decoder(decoder) -> bool:
+    return hasattr(next(decoder.children()), "in_features")  # :18-20
+
+
+def _compute_jacobian_vector_product(decoder, z: torch.Tensor, direction: torch.Tensor) -> torch.Tensor:
+    """J(z) * direction by autograd (:12-35) -- generic path, any nn.Module."""
+    z = z.requires_grad_(True)
+    flat = _is_flat_decoder(decoder)
+
+    def decode_to_image(p):
+        if not flat and p.ndim == 2:
+            p = p.unsqueeze(-1).unsqueeze(-1)
+        img = torch.sigmoid(decoder(p))
+        return img.view(img.size(0), -1)
+
+    _, out = torch.autograd.functional.jvp(decode_to_image, (z,), (direction,))
+    return out
+
+
+@contextlib.contextmanager
+def _strict_fp32():
+    """1e-5 parity needs true fp32 convolutions/matmuls (no TF32)."""
+    a, b = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        yield
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = a, b
+
+
+# ------------------------------------------------------------ explicit forward mode
+def _flatten_layers(decoder):
+    """Layer list of a conv decoder, or None if it contains something we do not know."""
+    out = []
+
+    def walk(m):
+        if isinstance(m, nn.Sequential):
+            for c in m:
+                if not walk(c):
+                    return False
+            return True
+        if isinstance(m, (nn.Conv2d, nn.ConvTranspose2d, nn.BatchNorm2d, nn.GroupNorm, nn.ReLU, nn.Identity)):
+            out.append(m)
+            return True
+        return False
+
+    kids = list(decoder.children())
+    # SpatialDecoder.forward = deconv_layers(conv_in(z)): children order == execution order
+    if not kids or not hasattr(decoder, "conv_in") or not hasattr(decoder, "deconv_layers") or len(kids) != 2:
+        return None
+    for k in kids:
+        if not walk(k):
+            return None
+    return out
+
+
+def _conv_pair(m, x, t):
+    """(primal, tangent) through a linear layer with one library call; bias only on the primal."""
+    n = x.shape[0]
+    xt = torch.cat([x, t], 0)
+    if isinstance(m, nn.Conv2d):
+        y = F.conv2d(xt, m.weight, None, m.stride, m.padding, m.dilation, m.groups)
+    else:
+        y = F.conv_transpose2d(xt, m.weight, None, m.stride, m.padding, m.output_padding, m.groups, m.dilation)
+    yp, yt = y[:n], y[n:]
+    if m.bias is not None:
+        yp = yp + m.bias.view(1, -1, 1, 1)
+    return yp, yt
+
+
+def _bn_pair(m, x, t, groups):
+    """BatchNorm2d forward-mode.  Train mode: statistics per group of rows (= one reference batch)."""
+    C = x.shape[1]
+    w = m.weight.view(1, 1, C, 1, 1) if m.weight is not None else 1.0
+    b = m.bias.view(1, 1, C, 1, 1) if m.bias is not None else 0.0
+    if m.training or m.running_mean is None:
+        xg = x.view(groups, -1, *x.shape[1:])
+        tg = t.view(groups, -1, *t.shape[1:])
+        mu = xg.mean(dim=(1, 3, 4), keepdim=True)
+        xc = xg - mu
+        var = (xc * xc).mean(dim=(1, 3, 4), keepdim=True)  # biased, as F.batch_norm normalises
+        r = torch.rsqrt(var + m.eps)
+        xh = xc * r
+        tc = tg - tg.mean(dim=(1, 3, 4), keepdim=True)
+        th = r * (tc - xh * (xh * tg).mean(dim=(1, 3, 4), keepdim=True))
+        return (xh * w + b).view_as(x), (th * w).view_as(t)
+    r = torch.rsqrt(m.running_var + m.eps).view(1, C, 1, 1)
+    w4 = m.weight.view(1, C, 1, 1) if m.weight is not None else 1.0
+    b4 = m.bias.view(1, C, 1, 1) if m.bias is not None else 0.0
+    return (x - m.running_mean.view(1, C, 1, 1)) * r * w4 + b4, t * r * w4
+
+
+def _gn_pair(m, x, t):
+    """GroupNorm forward-mode (per-sample statistics)."""
+    n, C = x.shape[:2]
+    xg = x.reshape(n, m.num_groups, -1)
+    tg = t.reshape(n, m.num_groups, -1)
+    mu = xg.mean(-1, keepdim=True)
+    xc = xg - mu
+    r = torch.rsqrt((xc * xc).mean(-1, keepdim=True) + m.eps)
+    xh = xc * r
+    th = r * (tg - tg.mean(-1, keepdim=True) - xh * (xh * tg).mean(-1, keepdim=True))
+    xh, th = xh.view_as(x), th.view_as(t)
+    if m.affine:
+        w, b = m.weight.view(1, C, 1, 1), m.bias.view(1, C, 1, 1)
+        return xh * w + b, th * w
+    return xh, th
+
+
+def _forward_mode(layers, z, dz, groups):
+    """sigmoid(decoder(z)) tangent for rows z (R,C) with direction dz; returns (R,P)."""
+    x, t = z[:, :, None, None], dz[:, :, None, None]
+    for m in layers:
+        if isinstance(m, (nn.Conv2d, nn.ConvTranspose2d)):
+            x, t = _conv_pair(m, x, t)
+        elif isinstance(m, nn.BatchNorm2d):
+            x, t = _bn_pair(m, x, t, groups)
+        elif isinstance(m, nn.GroupNorm):
+            x, t = _gn_pair(m, x, t)
+        elif isinstance(m, nn.ReLU):
+            t = t * (x > 0)
+            x = torch.relu(x)
+    s = torch.sigmoid(x)  # always applied (:29)
+    return (s * (1 - s) * t).reshape(z.shape[0], -1)
+
+
+@torch.no_grad()
+def edge_lengths_device(decoder, z_flat, ei, ej, batch_size=512, pos_ij=None, pos_ji=None, csr_data=None,
+                        e_lo=0, e_hi=None, groups_per_call=64):
+    """Edge lengths for edges [e_lo,e_hi) of the (ei,ej) list, all tensors on the decoder's CUDA device.
+
+    Batches are the reference's: consecutive `batch_size` edges of the GLOBAL list, so e_lo must be a
+    multiple of batch_size (multi-GPU sharding keeps whole batches).  Returns len f32[e_hi-e_lo]; when
+    csr_data/pos_* are given the lengths are also scattered to both CSR directions.
+    """
+    E = ei.numel()
+    e_hi = E if e_hi is None else e_hi
+    assert e_lo % batch_size == 0
+    dev = z_flat.device
+    out = torch.empty(max(e_hi - e_lo, 0), dtype=torch.float32, device=dev)
+    layers = None if _is_flat_decoder(decoder) else _flatten_layers(decoder)
+    with _strict_fp32():
+        lo = e_lo
+        while lo < e_hi:
+            full = (e_hi - lo) // batch_size
+            if layers is not None and full >= 1:
+                g = min(full, groups_per_call)
+                hi = lo + g * batch_size
+            else:
+                g, hi = 1, min(lo + batch_size, e_hi)
+            a = z_flat[ei[lo:hi].long()]
+            b = z_flat[ej[lo:hi].long()]
+            d = b - a
+            if layers is not None:
+                # start- and end-point JVPs are separate decoder calls in the reference => separate BN groups
+                j = _forward_mode(layers, torch.cat([a, b], 0), torch.cat([d, d], 0), 2 * g)
+                ja, jb = j[: hi - lo].contiguous(), j[hi - lo:].contiguous()
+            else:
+                with torch.enable_grad():
+                    ja = _compute_jacobian_vector_product(decoder, a.clone(), d).contiguous()
+                    jb = _compute_jacobian_vector_product(decoder, b.clone(), d).contiguous()
+            dg.edge_len_scatter(ja.float(), jb.float(), lo - e_lo, None, None, out, None)
+            if csr_data is not None:
+                dg.edge_len_scatter(ja.float(), jb.float(), lo, pos_ij, pos_ji, None, csr_data)
+            lo = hi
+    return out
+
+
+@torch.no_grad()
+def edge_lengths_riemannian(decoder, z_start: torch.Tensor, z_end: torch.Tensor, batch_size: int = 512) -> torch.Tensor:
+    """Calculate Riemannian edge lengths between latent points (:37-66).
+
+    Returns float32 (E,) on the decoder's device.  A CPU-resident decoder is copied to the GPU for the
+    computation (there is no CPU path) and the result is moved back to its device."""
+    assert z_start.shape == z_end.shape, "Start and end points must have same shape"  # :40
+    home = next(decoder.parameters()).device  # :42
+    dev = _lib.require_cuda()
+    dec = decoder if home.type == "cuda" else copy.deepcopy(decoder).to(dev)
+    dev = next(dec.parameters()).device
+    E = z_start.size(0)
+    if E == 0:
+        return torch.empty(0, dtype=torch.float32, device=home)
+    # stack start/end rows as a 2E-row table so the shared device routine can index it
+    table = torch.cat([z_start.to(dev, torch.float32), z_end.to(dev, torch.float32)], 0).contiguous()
+    ei = torch.arange(E, device=dev, dtype=torch.int32)
+    ej = ei + E
+    out = edge_lengths_device(dec, table, ei, ej, batch_size=batch_size)
+    return out.to(home).to(torch.float32)

@@ -1,0 +1,159 @@
+"""Device-resident stage driver behind the `build_codebook` CLI (reference:
+src/scripts/build_codebook.py:31-76).  Latents go to HBM once; every stage consumes and
+produces device tensors; host arrays are materialised only for the artifacts.
+
+Multi-GPU (one process per GPU, torch.distributed): kNN query rows and whole 512-edge
+JVP batches are split across ranks and all-gathered; graph construction and the
+(inherently sequential) k-means++ chain are replicated -- they are a few percent of the
+build and need no communication that way.
+"""
+from __future__ import annotations
+
+import time
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from . import _lib
+from . import device_graph as dg
+from .geo.knn_graph_optimized import knn_graph_device
+from .geo.riemannian_metric import edge_lengths_device
+from .geo.kmeans_optimized import fit_kmedoids_optimized
+
+
+def _dist_info(group):
+    import torch.distributed as dist
+    if group is None and not (dist.is_available() and dist.is_initialized()):
+        return None, 0, 1
+    return dist, dist.get_rank(group), dist.get_world_size(group)
+
+
+def shard_range(total, rank, world, multiple=1):
+    """Contiguous [lo,hi) of `total` items for `rank`, boundaries at multiples of `multiple`."""
+    units = -(-total // multiple)
+    per, extra = divmod(units, world)
+    lo_u = rank * per + min(rank, extra)
+    hi_u = lo_u + per + (1 if rank < extra else 0)
+    return min(lo_u * multiple, total), min(hi_u * multiple, total)
+
+
+def all_gather_rows(x, total_rows, world, rank, group, dist, multiple=1):
+    """Concatenate per-rank row shards (shard_range layout) into the full tensor on every rank."""
+    if world == 1:
+        return x
+    sizes = [shard_range(total_rows, r, world, multiple) for r in range(world)]
+    mx = max(hi - lo for lo, hi in sizes)
+    pad = torch.zeros((mx,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+    pad[: x.shape[0]] = x
+    bufs = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(bufs, pad, group=group)
+    return torch.cat([b[: hi - lo] for b, (lo, hi) in zip(bufs, sizes)], 0)
+
+
+@dataclass
+class BuildResult:
+    z_flat: torch.Tensor
+    g_euc: dg.DeviceCSR
+    g_geo: dg.DeviceCSR
+    g_lcc: dg.DeviceCSR
+    ei: torch.Tensor
+    ej: torch.Tensor
+    edge_len: torch.Tensor
+    mask: torch.Tensor  # uint8[M]
+    medoids: np.ndarray
+    assign: np.ndarray
+    qe: float
+    codes: np.ndarray
+    timings: dict = field(default_factory=dict)
+
+
+class _Timer:
+    def __init__(self):
+        self.t = {}
+
+    def __call__(self, name):
+        torch.cuda.synchronize()
+        now = time.perf_counter()
+        if hasattr(self, "_last"):
+            self.t[self._last_name] = now - self._last
+        self._last, self._last_name = now, name
+
+    def stop(self):
+        self.__call__("_end")
+        self.t.pop("_end", None)
+        return self.t
+
+
+def build_codebook_device(z4: torch.Tensor, decoder, k=20, sym="union", K=512, init="kpp", seed=42, batch_size=512,
+                          group=None, verbose=True) -> BuildResult:
+    """Everything between loading the inputs and writing the artifacts."""
+    dev = _lib.require_cuda()
+    dist, rank, world = _dist_info(group)
+    N, C, H, Wd = z4.shape
+    tm = _Timer()
+    tm("h2d")
+    z_flat = z4.to(dev, torch.float32).permute(0, 2, 3, 1).reshape(-1, C).contiguous()  # :35
+    M = z_flat.shape[0]
+    if M < 2:
+        raise ValueError("need at least two latent vectors")
+    k_eff = max(1, min(k, M - 1))
+    # ---- kNN + symmetrise (knn_graph_optimized.py) ----
+    tm("knn")
+    if world == 1:
+        g_euc, _, _ = knn_graph_device(z_flat, k_eff, "connectivity", sym)
+    else:
+        lo, hi = shard_range(M, rank, world)
+        idx, dst, _ = dg.knn_topk(z_flat, k_eff + 1, lo, hi)
+        idx = all_gather_rows(idx, M, world, rank, group, dist)
+        dst = all_gather_rows(dst, M, world, rank, group, dist)
+        me = torch.arange(M, device=dev, dtype=torch.int32)
+        if bool((idx[:, 0] == me).all()):
+            idx = idx[:, 1:].contiguous()
+        else:
+            keep = torch.ones_like(idx, dtype=torch.bool).scatter_(1, dst.argmin(dim=1, keepdim=True), False)
+            idx = idx[keep].view(M, -1).contiguous()
+        if sym not in ("mutual", "union"):
+            raise ValueError(f"Invalid symmetry mode: {sym}")
+        g_euc = dg.symmetrize(idx, None, sym)
+    # ---- upper-triangular edges in row-major order (build_codebook.py:43-45) ----
+    tm("edges")
+    ei, ej, pos_ij, pos_ji = dg.upper_edges(g_euc)
+    E = ei.numel()
+    if verbose and rank == 0:
+        print(f"Re-weighting {E} edges using Riemannian metric...")
+    # ---- Riemannian lengths, scattered into both CSR directions (:51-54) ----
+    tm("edge_len")
+    g_geo = dg.DeviceCSR(g_euc.indptr, g_euc.indices, torch.zeros_like(g_euc.data), M)
+    if world == 1:
+        L = edge_lengths_device(decoder, z_flat, ei, ej, batch_size, pos_ij, pos_ji, g_geo.data)
+    else:
+        lo, hi = shard_range(E, rank, world, multiple=batch_size)
+        Lp = edge_lengths_device(decoder, z_flat, ei, ej, batch_size, e_lo=lo, e_hi=hi)
+        L = all_gather_rows(Lp, E, world, rank, group, dist, multiple=batch_size)
+        g_geo.data[pos_ij] = L
+        g_geo.data[pos_ji] = L
+    # ---- largest connected component (:56-63) ----
+    tm("lcc")
+    mask, new_id, n_keep, _ = dg.largest_component(g_geo)
+    if n_keep < M:
+        if verbose and rank == 0:
+            print(f"Using LCC: {n_keep}/{M} nodes")
+        g_lcc = dg.compact(g_geo, mask, new_id, n_keep)
+    else:
+        g_lcc = g_geo
+        mask = torch.ones(M, dtype=torch.uint8, device=dev)
+    # ---- K-medoids (:70) ----
+    tm("kmedoids")
+    if verbose and rank == 0:
+        medoids, assign, qe = fit_kmedoids_optimized(g_lcc, K=K, init=init, seed=seed)
+    else:
+        import contextlib
+        import io
+        with contextlib.redirect_stdout(io.StringIO()):
+            medoids, assign, qe = fit_kmedoids_optimized(g_lcc, K=K, init=init, seed=seed)
+    tm("codes")
+    codes = np.full(M, -1, dtype=np.int32)  # :74-76
+    codes[mask.cpu().numpy().astype(bool)] = assign
+    t = tm.stop()
+    return BuildResult(z_flat, g_euc, g_geo, g_lcc, ei, ej, L, mask, medoids, assign, qe, codes.reshape(N, H, Wd), t)
