@@ -1,0 +1,315 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json metric: codebook build seconds & SSSP edge-relax/s (2.94M latents, K=512).
+
+    python bench.py --gpus N --steps K --warmup W            (N>1: launched by torch.distributed.run)
+    python bench.py --impl reference ...                      (reference CPU implementation, bounded sample)
+
+Workload (configs[1]): z = randn(60000,16,7,7; seed 42) -> 2.94M latents d=16, random-init FashionMNIST
+spatial decoder (seed 0, BN train mode), k=20 union kNN, Riemannian edge lengths, LCC, K=512 kpp seed 42.
+Setup runs the whole codebook build once on the GPU (reported under "build", seconds per stage); a timed
+"step" is then one `dijkstra_multi_source`-shaped call: S=--sources-per-step independent SSSPs on that graph.
+  value = ranks * S * nnz / t      directed-edge relaxations per second (each edge once per source)
+  e2e   = same call from pinned HOST buffers (CSR upload + SSSP + D[S,n] float32 download in the timed region)
+Inputs (the graph, 0.8 GB) exceed the 126 MB L2, so no explicit L2 flush is needed between steps.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+FASHION_CFG = dict(in_channels=1, output_image_size=28, latent_dim=16, enc_channels=[64, 128, 256],
+                   dec_channels=[256, 128, 64], recon_loss="mse", norm_type="batch", mse_use_sigmoid=True)
+METRIC = "sssp_edge_relax_per_s"
+UNIT = "edge-relax/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=6)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--images", type=int, default=60000, help="N of the (N,16,7,7) latent tensor")
+    ap.add_argument("--grid", type=int, default=7)
+    ap.add_argument("--sources-per-step", type=int, default=64)
+    ap.add_argument("--slots", type=int, default=0, help="concurrent sources per launch (0 = auto)")
+    ap.add_argument("--K", type=int, default=512)
+    ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--ref-latents", type=int, default=100000, help="reference arm: size of the latent subsample")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.idx = [], None, str(gpu_index)
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", self.idx], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 8 for n, v in zip(names, r[4:8]) if v.lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ reference arm
+def _dijkstra_chunk(args):
+    from scipy.sparse.csgraph import dijkstra
+    W, src = args
+    D = dijkstra(csgraph=W, directed=False, indices=src)
+    return float(np.asarray(D, dtype=np.float32)[:, ::4096].sum())
+
+
+def cpu_dijkstra_rate(W, sources, workers):
+    """Reference SSSP (scipy Dijkstra, as geo_shortest_paths.py:36-49 calls it) over `workers` processes."""
+    import multiprocessing as mp
+    chunks = [c for c in np.array_split(np.asarray(sources), workers) if len(c)]
+    t0 = time.perf_counter()
+    if len(chunks) == 1:
+        _dijkstra_chunk((W, chunks[0]))
+    else:
+        with mp.get_context("fork").Pool(len(chunks)) as pool:
+            pool.map(_dijkstra_chunk, [(W, c) for c in chunks])
+    dt = time.perf_counter() - t0
+    return len(sources) * W.nnz / dt, dt
+
+
+def run_reference(a):
+    """The reference's own CPU path (sklearn kNN + scipy Dijkstra through oracle/geo_oracle.py, which calls the
+    same library entry points as src/geo/*) on a bounded sample; rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    sys.path.insert(0, str(ROOT / "oracle"))
+    import torch
+    import geo_oracle as oracle
+    cores = len(os.sched_getaffinity(0))
+    M = a.ref_latents
+    z = torch.randn(a.images, 16, a.grid, a.grid, generator=torch.Generator().manual_seed(42))
+    zf = z.permute(0, 2, 3, 1).reshape(-1, 16)[:M].numpy()
+    t0 = time.perf_counter()
+    W, _ = oracle.knn_graph(zf, k=20, mode="distance", sym="union")  # Euclidean weights: CPU JVPs would take hours
+    t_knn = time.perf_counter() - t0
+    W = oracle.check_graph(W)
+    workers = max(1, min(cores, 64))
+    per_step = workers  # one source per worker per step keeps a step at a few seconds
+    rng = np.random.RandomState(0)
+    times = []
+    for i in range(a.warmup + a.steps):
+        src = rng.choice(M, per_step, replace=False)
+        rate, dt = cpu_dijkstra_rate(W, src, workers)
+        if i >= a.warmup:
+            times.append(dt)
+    t = float(np.sum(times))
+    value = a.steps * per_step * W.nnz / t
+    sample = (f"{per_step} sources/step on the union kNN graph (k=20, Euclidean weights) of the first {M} of "
+              f"{a.images * a.grid * a.grid} latents, n={M}, nnz={W.nnz}; sklearn kNN took {t_knn:.1f}s (untimed)")
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": 1e3 * t / a.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "FashionMNIST-shape geodesic codebook: 60k x 7 x 7 = 2.94M latents d=16, k=20 union, K=512, seed 42",
+                       "sources_per_step": per_step, "sample": sample},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": workers, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ B200 arm
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+    from vqvae_b200 import _lib, device_graph as dg
+    from vqvae_b200.models import SpatialVAE
+    from vqvae_b200.pipeline import build_codebook_device
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.load()
+
+    # ---- setup: the whole codebook build, once (this IS the first half of the metric) ----
+    z4 = torch.randn(a.images, 16, a.grid, a.grid, generator=torch.Generator().manual_seed(42))
+    torch.manual_seed(0)
+    decoder = SpatialVAE(**FASHION_CFG).decoder.to(dev)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    res = build_codebook_device(z4, decoder, k=20, sym="union", K=a.K, init="kpp", seed=42, batch_size=512,
+                                verbose=False)
+    torch.cuda.synchronize()
+    build_total = time.perf_counter() - t0
+    g = res.g_lcc
+    n, nnz = g.n, g.nnz
+    del z4
+    S = a.sources_per_step
+    slots = a.slots if a.slots > 0 else dg.default_slots(n)
+    slots = max(1, min(slots, S, 32))
+    row_ptr, adj, mean_w = g.adjacency(False)
+    rng = np.random.RandomState(1234 + rank)
+    D = torch.empty((S, n), dtype=torch.float32, device=dev)
+    launches_per_step = -(-S // slots)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_sources(i):
+        # medoids first (the K-source assignment call of kmeans_optimized.py:97), then seeded random vertices
+        lo = (i * S) % max(1, len(res.medoids))
+        src = np.asarray(res.medoids[lo:lo + S], dtype=np.int64)
+        if len(src) < S:
+            src = np.r_[src, rng.choice(n, S - len(src), replace=False)]
+        return src
+
+    # ---- device-resident timing ----
+    for i in range(a.warmup):
+        dg.sssp_multi(g, step_sources(i), slots=slots, out=D)
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stats_tot = dict(relaxations=0, rounds=0, scans=0)
+    ev0.record()
+    for i in range(a.steps):
+        _, st = dg.sssp_multi(g, step_sources(a.warmup + i), slots=slots, out=D, stats=True)
+        for k_ in stats_tot:
+            stats_tot[k_] += st[k_]
+    ev1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms = ev0.elapsed_time(ev1)
+    t_all = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_all, op=dist.ReduceOp.MAX)
+    ms = float(t_all.item())
+    value = world * a.steps * S * nnz / (ms * 1e-3)
+
+    # ---- end-to-end through host buffers (pinned): upload CSR, SSSP, download D ----
+    e2e = None
+    if not a.skip_e2e:
+        h_indptr = g.indptr.cpu().pin_memory()
+        h_indices = g.indices.cpu().pin_memory()
+        h_data = g.data.cpu().pin_memory()
+        h_D = torch.empty((S, n), dtype=torch.float32).pin_memory()
+
+        def e2e_step(i):
+            gg = dg.DeviceCSR(h_indptr.to(dev, non_blocking=True), h_indices.to(dev, non_blocking=True),
+                              h_data.to(dev, non_blocking=True), n)
+            Dd = dg.sssp_multi(gg, step_sources(i), slots=slots, out=D)
+            h_D.copy_(Dd, non_blocking=True)
+            torch.cuda.synchronize()
+            return float(h_D[0, 0])
+
+        for i in range(min(a.warmup, 2)):
+            e2e_step(i)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(a.steps):
+            e2e_step(a.warmup + i)
+        e1.record()
+        barrier()
+        t2 = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * a.steps * S * nnz / (float(t2.item()) * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": int(h_indptr.numel() * 8 + h_indices.numel() * 4 + h_data.numel() * 4 + S * 4),
+               "d2h_bytes_per_step": int(S * n * 4), "ms_per_step": float(t2.item()) / a.steps}
+        del h_D
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    # ---- roofline of the dominant kernel (sssp_kernel): algorithmic bytes per launch / mean launch time ----
+    peaks = {}
+    try:
+        peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    bytes_per_launch = slots * 16.0 * (nnz + n)  # 16 B per directed edge + 16 B per vertex, per source
+    n_launch = a.steps * launches_per_step
+    launch_ms = ms / n_launch
+    achieved = bytes_per_launch / (launch_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        traffic = json.loads((ROOT / "profiles" / "sssp_traffic.json").read_text()).get("dram_bytes_per_launch")
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+                "kernel": "sssp_kernel", "launch_ms": launch_ms, "algorithmic_bytes_per_launch": bytes_per_launch,
+                "relaxations_per_algorithmic_edge": stats_tot["relaxations"] / (a.steps * S * nnz)}
+    # ---- CPU baseline: scipy Dijkstra on the very same graph, bounded sample ----
+    cpu = None
+    if not a.skip_cpu_baseline and world == 1:
+        sys.path.insert(0, str(ROOT / "oracle"))
+        import geo_oracle as oracle
+        W = oracle.check_graph(g.to_scipy())
+        cores = len(os.sched_getaffinity(0))
+        workers = max(1, min(cores, 2 if n > 1_000_000 else 8))
+        src = step_sources(0)[:workers]
+        rate, dt = cpu_dijkstra_rate(W, src, workers)
+        # parity spot check on the timed sample's first source
+        d_ref = oracle.sssp_multi(W, src[:1])
+        d_gpu = dg.sssp_multi(g, src[:1]).cpu().numpy()
+        cpu = {"value": rate, "unit": UNIT, "cores": workers, "kind": "port",
+               "sample": f"{len(src)} sources of the same graph (n={n}, nnz={nnz}), one scipy Dijkstra per process, {dt:.1f}s",
+               "host_cores_available": cores, "bit_equal_to_gpu": bool(np.array_equal(d_ref, d_gpu))}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "FashionMNIST-shape geodesic codebook: 60k x 7 x 7 = 2.94M latents d=16, k=20 union, K=512, seed 42",
+                       "latents": int(res.z_flat.shape[0]), "n": n, "nnz": nnz, "sources_per_step": S, "slots": slots,
+                       "delta": mean_w, "l2": "inputs larger than L2 (graph 0.8 GB)", "parallelism": f"sources x{world}"},
+            "build": {"total_s": build_total, **{k_: round(v, 4) for k_, v in res.timings.items()}, "qe": res.qe,
+                      "medoids_head": [int(x) for x in res.medoids[:5]]},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": n_launch, "clocks": clocks,
+            "sssp_stats": {k_: int(v) for k_, v in stats_tot.items()}}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
