@@ -149,12 +149,13 @@ __global__ void cc_init_kernel(int32_t* label, int64_t n) {
 __global__ void cc_hook_kernel(const int64_t* indptr, const int32_t* col, int64_t n, int32_t* label, int* changed) {
     const int64_t u = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
     const int lane = threadIdx.x & 7;
-    if (u >= n) return;
-    const int32_t lu = ld_cg_s32(label + u);
+    const bool live = u < n;  // no early return: every lane of the warp takes part in the shuffles
+    const int32_t lu = live ? ld_cg_s32(label + u) : 0;
     int32_t m = lu;
-    for (int64_t p = indptr[u] + lane; p < indptr[u + 1]; p += 8) m = min(m, ld_cg_s32(label + col[p]));
+    if (live)
+        for (int64_t p = indptr[u] + lane; p < indptr[u + 1]; p += 8) m = min(m, ld_cg_s32(label + col[p]));
     for (int o = 4; o; o >>= 1) m = min(m, __shfl_xor_sync(0xffffffffu, m, o, 8));
-    if (lane == 0 && m < lu) {
+    if (live && lane == 0 && m < lu) {
         atomicMin(label + lu, m);
         atomicMin(label + u, m);
         *changed = 1;

@@ -116,6 +116,8 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
 
     unsigned n_relax = 0, n_improve = 0, n_rounds = 0, n_scans = 0;
     const int lane = threadIdx.x & (kGroup - 1);
+    // the two 16-lane groups of a warp run different trip counts: shuffles must name only their own lanes
+    const unsigned gmask = 0xFFFFu << (threadIdx.x & 16);
     const int64_t ggroup = gtid / kGroup;
     const int64_t ngroups = gthreads / kGroup;
 
@@ -147,7 +149,7 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
                 __threadfence();
                 du = __longlong_as_double((long long)ld_cg_u64(dist_s + u));
             }
-            du = __shfl_sync(0xffffffffu, du, 0, kGroup);
+            du = __shfl_sync(gmask, du, 0, kGroup);
             const double thr = __longlong_as_double((long long)ld_cg_u64((const unsigned long long*)&p.ctl[s].thr));
             const int64_t beg = p.row_ptr[u] >> 1, end = p.row_ptr[u + 1] >> 1;
             uint32_t* qnext = p.queue[par ^ 1] + base;
@@ -260,7 +262,7 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
                         if ((unsigned long long)__double_as_longlong(c1) == dv && (int)e.z < best) best = (int)e.z;
                     }
                 }
-                for (int o = kGroup / 2; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o, kGroup));
+                for (int o = kGroup / 2; o; o >>= 1) best = min(best, __shfl_xor_sync(gmask, best, o, kGroup));
                 if (lane == 0) p.out_pred[item] = best == 0x7fffffff ? -9999 : best;
             }
         }
