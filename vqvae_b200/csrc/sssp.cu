@@ -27,9 +27,13 @@ constexpr int kGroup = 16;  // lanes cooperating on one vertex (16 x uint4 = 32 
 struct SlotCtl {
     double thr;                  // current near/far threshold
     unsigned long long far_min;  // min dist bits over dirty vertices (phase B1)
-    int cnt[3];                  // queue sizes, rotating: round r reads cnt[r%3], fills cnt[(r+1)%3], clears cnt[(r+2)%3]
+    int active[3];               // "something was queued for this slot", rotating like GlobalCtl::qcount
     int done;
     int pad[2];
+};
+struct GlobalCtl {
+    int qcount[3];  // combined queue sizes: round r reads [r%3], fills [(r+1)%3], clears [(r+2)%3]
+    int pad;
 };
 
 struct SsspParams {
@@ -40,8 +44,9 @@ struct SsspParams {
     double delta;
     unsigned long long* dist;  // [nslots][n]
     int* state;                // [nslots][n]  0 clean, 1 dirty (far), 2 queued (near)
-    uint32_t* queue[2];        // [nslots][n] each
+    uint32_t* queue[2];        // combined work lists, entries (slot << 27) | vertex, capacity nslots*n each
     SlotCtl* ctl;              // [nslots]
+    GlobalCtl* gctl;
     unsigned long long* stats; // [4]
     // full-SSSP mode
     const int32_t* sources;  // [nslots]
@@ -54,8 +59,37 @@ struct SsspParams {
     int32_t* label;
 };
 
+constexpr int kVertexBits = 27;
+constexpr uint32_t kVertexMask = (1u << kVertexBits) - 1;
+constexpr int kStage = 128;  // per-warp staging entries before one aggregated global atomicAdd
+
+// queue push through the warp's shared-memory staging buffer (same-address global atomics on the queue
+// tail serialise in L2: ~1 cycle each, which capped the first version at 5 % of roofline)
+__device__ __forceinline__ void stage_push(uint32_t entry, uint32_t* wbuf, int* wcnt, uint32_t* qnext, int* qtail) {
+    const int pos = atomicAdd(wcnt, 1);
+    if (pos < kStage) wbuf[pos] = entry;
+    else qnext[atomicAdd(qtail, 1)] = entry;  // staging full (rare): straight to the global list
+}
+// warp-synchronous flush; every lane of the warp must call it
+__device__ __forceinline__ void stage_flush(uint32_t* wbuf, int* wcnt, uint32_t* qnext, int* qtail, int min_fill) {
+    __syncwarp();
+    int cnt = *(volatile int*)wcnt;
+    if (cnt >= min_fill && cnt > 0) {
+        cnt = cnt < kStage ? cnt : kStage;
+        const int wl = threadIdx.x & 31;
+        int base = 0;
+        if (wl == 0) base = atomicAdd(qtail, cnt);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        for (int i = wl; i < cnt; i += 32) qnext[base + i] = wbuf[i];
+        __syncwarp();
+        if (wl == 0) *(volatile int*)wcnt = 0;
+    }
+    __syncwarp();
+}
+
 __device__ __forceinline__ void relax_pair(uint32_t v, uint32_t wbits, double du, unsigned long long* dist_s,
-                                           int* state_s, double thr, uint32_t* qnext, int* cnt_next,
+                                           int* state_s, double thr, uint32_t slot_tag, unsigned& active_mask,
+                                           uint32_t* wbuf, int* wcnt, uint32_t* qnext, int* qtail,
                                            unsigned& n_improve) {
     double cand = du + (double)__uint_as_float(wbits);
     unsigned long long cb = (unsigned long long)__double_as_longlong(cand);
@@ -66,8 +100,8 @@ __device__ __forceinline__ void relax_pair(uint32_t v, uint32_t wbits, double du
             ++n_improve;
             if (cand < thr) {
                 if (atomicExch(state_s + v, 2) != 2) {
-                    int pos = atomicAdd(cnt_next, 1);
-                    qnext[pos] = v;
+                    active_mask |= 1u << (slot_tag >> kVertexBits);
+                    stage_push(slot_tag | v, wbuf, wcnt, qnext, qtail);
                 }
             } else {
                 atomicMax(state_s + v, 1);
@@ -82,9 +116,11 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
     const int B = p.nslots;
     const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
-    __shared__ int s_cnt[kMaxSlots + 1];
+    __shared__ int s_need[kMaxSlots];
     __shared__ int s_flag, s_alldone;
     __shared__ unsigned long long s_red[kThreads / 32];
+    __shared__ uint32_t s_stage[kThreads / 32][kStage];
+    __shared__ int s_stage_n[kThreads / 32];
 
     // ---- init ----
     if (!p.voronoi) {
@@ -93,6 +129,12 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
             p.state[i] = 0;
         }
     }
+    if (threadIdx.x < kThreads / 32) s_stage_n[threadIdx.x] = 0;
+    if (gtid == 0) {
+        p.gctl->qcount[0] = 0;
+        p.gctl->qcount[1] = 0;
+        p.gctl->qcount[2] = 0;
+    }
     grid.sync();
     if (gtid < B) {
         int s = (int)gtid;
@@ -100,15 +142,13 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
         SlotCtl c;
         c.thr = p.delta;
         c.far_min = D64_INF_BITS;
-        c.cnt[0] = 0;
-        c.cnt[1] = 0;
-        c.cnt[2] = 0;
+        c.active[0] = c.active[1] = c.active[2] = 0;
         c.done = 0;
         unsigned long long old = atomicMin(p.dist + (int64_t)s * n + src, 0ULL);
         if (old != 0ULL) {  // (voronoi: re-inserting an existing centre changes nothing)
             p.state[(int64_t)s * n + src] = 2;
-            p.queue[0][(int64_t)s * n] = (uint32_t)src;
-            c.cnt[0] = 1;
+            p.queue[0][atomicAdd(&p.gctl->qcount[0], 1)] = ((uint32_t)s << kVertexBits) | (uint32_t)src;
+            c.active[0] = 1;
         }
         p.ctl[s] = c;
     }
@@ -116,51 +156,84 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
 
     unsigned n_relax = 0, n_improve = 0, n_rounds = 0, n_scans = 0;
     const int lane = threadIdx.x & (kGroup - 1);
-    // the two 16-lane groups of a warp run different trip counts: shuffles must name only their own lanes
+    const int wlane = threadIdx.x & 31;
+    const int grp = (threadIdx.x >> 4) & 1;
+    // the two 16-lane groups of a warp may hold different items: shuffles name only their own lanes
     const unsigned gmask = 0xFFFFu << (threadIdx.x & 16);
-    const int64_t ggroup = gtid / kGroup;
-    const int64_t ngroups = gthreads / kGroup;
+    const int64_t gwarp = gtid >> 5;
+    const int64_t nwarps = gthreads >> 5;
+    uint32_t* wbuf = s_stage[threadIdx.x >> 5];
+    int* wcnt = &s_stage_n[threadIdx.x >> 5];
 
     for (int round = 0;; ++round) {
-        const int par = round & 1;            // queue buffer parity
+        const int par = round & 1;  // queue buffer parity
         const int c_cur = round % 3, c_next = (round + 1) % 3, c_clear = (round + 2) % 3;
-        if (gtid < B) {  // safe: both were last touched before the previous grid.sync
-            p.ctl[gtid].cnt[c_clear] = 0;
+        if (gtid < B) {  // safe: all of these were last touched before the previous grid.sync
+            p.ctl[gtid].active[c_clear] = 0;
             p.ctl[gtid].far_min = D64_INF_BITS;
         }
-        // ---- phase A: relax every queued vertex ----
-        if (threadIdx.x <= B) {
-            int acc = 0;
-            for (int s = 0; s < (int)threadIdx.x; ++s) acc += ld_cg_s32(&p.ctl[s].cnt[c_cur]);
-            s_cnt[threadIdx.x] = acc;  // exclusive prefix; s_cnt[B] = total
+        if (gtid == 0) p.gctl->qcount[c_clear] = 0;
+        // ---- phase A0: un-queue every listed vertex (state 2 -> 0) before any distance is read, so that a
+        //      later improvement of the same vertex re-queues it; the grid.sync replaces a per-item fence ----
+        const int total = ld_cg_s32(&p.gctl->qcount[c_cur]);
+        for (int64_t i = gtid; i < total; i += gthreads) {
+            const uint32_t entry = p.queue[par][i];
+            p.state[(int64_t)(entry >> kVertexBits) * n + (entry & kVertexMask)] = 0;
         }
-        __syncthreads();
-        const int total = s_cnt[B];
-        for (int64_t item = ggroup; item < total; item += ngroups) {
-            int s = 0;
-            while (s + 1 < B && item >= s_cnt[s + 1]) ++s;
-            const int64_t base = (int64_t)s * n;
-            unsigned long long* dist_s = p.dist + base;
-            int* state_s = p.state + base;
-            const uint32_t u = p.queue[par][base + (item - s_cnt[s])];
-            double du = 0.0;
-            if (lane == 0) {
-                atomicExch(state_s + u, 0);
-                __threadfence();
-                du = __longlong_as_double((long long)ld_cg_u64(dist_s + u));
+        grid.sync();
+        // ---- phase A: relax every queued (slot, vertex).  Each 16-lane group prefetches a chunk of `chunk`
+        //      items (entry, dist[u], row bounds, threshold: independent loads, one per lane) and then walks
+        //      them; the trip count is uniform per warp so the staging flush can be warp-synchronous ----
+        uint32_t* qnext = p.queue[par ^ 1];
+        int* qtail = &p.gctl->qcount[c_next];
+        unsigned active_mask = 0;
+        int chunk = 1;
+        while (chunk < kGroup && (int64_t)chunk * 2 * nwarps * 2 <= total) chunk <<= 1;
+        for (int64_t wbase = gwarp * 2 * chunk; wbase < total; wbase += nwarps * 2 * chunk) {
+            const int64_t my_item = wbase + (int64_t)grp * chunk + lane;
+            uint32_t entry = 0;
+            double du = 0.0, thr = 0.0;
+            int64_t beg = 0, end = 0;
+            if (lane < chunk && my_item < total) {
+                entry = p.queue[par][my_item];
+                const int s = (int)(entry >> kVertexBits);
+                const uint32_t u = entry & kVertexMask;
+                du = __longlong_as_double((long long)ld_cg_u64(p.dist + (int64_t)s * n + u));
+                thr = __longlong_as_double((long long)ld_cg_u64((const unsigned long long*)&p.ctl[s].thr));
+                beg = __ldg(p.row_ptr + u) >> 1;
+                end = __ldg(p.row_ptr + u + 1) >> 1;
             }
-            du = __shfl_sync(gmask, du, 0, kGroup);
-            const double thr = __longlong_as_double((long long)ld_cg_u64((const unsigned long long*)&p.ctl[s].thr));
-            const int64_t beg = p.row_ptr[u] >> 1, end = p.row_ptr[u + 1] >> 1;
-            uint32_t* qnext = p.queue[par ^ 1] + base;
-            int* cnt_next = &p.ctl[s].cnt[c_next];
-            for (int64_t i = beg + lane; i < end; i += kGroup) {
-                uint4 e = ld_stream_v4(p.adj4 + i);
-                n_relax += 2;
-                relax_pair(e.x, e.y, du, dist_s, state_s, thr, qnext, cnt_next, n_improve);
-                relax_pair(e.z, e.w, du, dist_s, state_s, thr, qnext, cnt_next, n_improve);
+            for (int j = 0; j < chunk; ++j) {
+                const uint32_t e_j = __shfl_sync(gmask, entry, j, kGroup);
+                const double du_j = __shfl_sync(gmask, du, j, kGroup);
+                const double thr_j = __shfl_sync(gmask, thr, j, kGroup);
+                const int64_t beg_j = __shfl_sync(gmask, beg, j, kGroup);
+                const int64_t end_j = __shfl_sync(gmask, end, j, kGroup);
+                const int64_t sbase = (int64_t)(e_j >> kVertexBits) * n;
+                unsigned long long* dist_s = p.dist + sbase;
+                int* state_s = p.state + sbase;
+                const uint32_t tag = e_j & ~kVertexMask;
+                for (int64_t i = beg_j + lane; i < end_j; i += 2 * kGroup) {
+                    // two 128-bit pair loads in flight per lane, then four distance gathers, then the updates
+                    const bool second = i + kGroup < end_j;
+                    const uint4 e0 = ld_stream_v4(p.adj4 + i);
+                    uint4 e1 = make_uint4(0, F32_INF_BITS, 0, F32_INF_BITS);
+                    if (second) e1 = ld_stream_v4(p.adj4 + i + kGroup);
+                    n_relax += second ? 4 : 2;
+                    relax_pair(e0.x, e0.y, du_j, dist_s, state_s, thr_j, tag, active_mask, wbuf, wcnt, qnext, qtail, n_improve);
+                    relax_pair(e0.z, e0.w, du_j, dist_s, state_s, thr_j, tag, active_mask, wbuf, wcnt, qnext, qtail, n_improve);
+                    if (second) {
+                        relax_pair(e1.x, e1.y, du_j, dist_s, state_s, thr_j, tag, active_mask, wbuf, wcnt, qnext, qtail, n_improve);
+                        relax_pair(e1.z, e1.w, du_j, dist_s, state_s, thr_j, tag, active_mask, wbuf, wcnt, qnext, qtail, n_improve);
+                    }
+                }
+                stage_flush(wbuf, wcnt, qnext, qtail, kStage / 2);
             }
         }
+        stage_flush(wbuf, wcnt, qnext, qtail, 1);
+        for (int o = 16; o; o >>= 1) active_mask |= __shfl_xor_sync(0xffffffffu, active_mask, o);
+        if (wlane == 0)
+            for (unsigned m = active_mask; m; m &= m - 1) *(volatile int*)&p.ctl[__ffs(m) - 1].active[c_next] = 1;
         grid.sync();
         ++n_rounds;
         // ---- control: which slots ran dry? (uniform across the grid) ----
@@ -168,8 +241,8 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
         __syncthreads();
         if (threadIdx.x < B) {
             int s = threadIdx.x;
-            int need = (!ld_cg_s32(&p.ctl[s].done)) && ld_cg_s32(&p.ctl[s].cnt[c_next]) == 0;
-            s_cnt[s] = need;
+            int need = (!ld_cg_s32(&p.ctl[s].done)) && ld_cg_s32(&p.ctl[s].active[c_next]) == 0;
+            s_need[s] = need;
             if (need) s_flag = 1;
         }
         __syncthreads();
@@ -178,19 +251,19 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
             ++n_scans;
             // ---- phase B1: min dist over dirty vertices of each dry slot ----
             for (int s = 0; s < B; ++s) {
-                if (!s_cnt[s]) continue;
-                const int64_t base = (int64_t)s * n;
+                if (!s_need[s]) continue;
+                const int64_t sbase = (int64_t)s * n;
                 unsigned long long m = D64_INF_BITS;
                 for (int64_t v = gtid; v < n; v += gthreads)
-                    if (ld_cg_s32(p.state + base + v) == 1) {
-                        unsigned long long d = ld_cg_u64(p.dist + base + v);
+                    if (ld_cg_s32(p.state + sbase + v) == 1) {
+                        unsigned long long d = ld_cg_u64(p.dist + sbase + v);
                         m = d < m ? d : m;
                     }
                 for (int o = 16; o; o >>= 1) {
                     unsigned long long t = __shfl_xor_sync(0xffffffffu, m, o);
                     m = t < m ? t : m;
                 }
-                if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = m;
+                if (wlane == 0) s_red[threadIdx.x >> 5] = m;
                 __syncthreads();
                 if (threadIdx.x == 0) {
                     for (int w = 1; w < kThreads / 32; ++w) m = s_red[w] < m ? s_red[w] : m;
@@ -199,27 +272,38 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
                 __syncthreads();
             }
             grid.sync();
-            // ---- phase B2: raise thr, queue dirty vertices below it ----
+            // ---- phase B2: raise thr, queue dirty vertices below it (ballot-aggregated tail bump) ----
             for (int s = 0; s < B; ++s) {
-                if (!s_cnt[s]) continue;
+                if (!s_need[s]) continue;
                 const unsigned long long fm = ld_cg_u64(&p.ctl[s].far_min);
                 if (fm == D64_INF_BITS) {  // nothing dirty: this source has converged
                     if (gtid == 0) p.ctl[s].done = 1;
                     continue;
                 }
                 const double thr_new = __longlong_as_double((long long)fm) + p.delta;
-                const int64_t base = (int64_t)s * n;
-                uint32_t* qnext = p.queue[par ^ 1] + base;
-                for (int64_t v = gtid; v < n; v += gthreads)
-                    if (ld_cg_s32(p.state + base + v) == 1) {
-                        double d = __longlong_as_double((long long)ld_cg_u64(p.dist + base + v));
-                        if (d < thr_new) {
-                            p.state[base + v] = 2;
-                            int pos = atomicAdd(&p.ctl[s].cnt[c_next], 1);
-                            qnext[pos] = (uint32_t)v;
+                const int64_t sbase = (int64_t)s * n;
+                const int64_t n_round = (n + 31) & ~(int64_t)31;
+                for (int64_t v = gtid; v < n_round; v += gthreads) {
+                    bool take = false;
+                    if (v < n && ld_cg_s32(p.state + sbase + v) == 1) {
+                        double d = __longlong_as_double((long long)ld_cg_u64(p.dist + sbase + v));
+                        take = d < thr_new;
+                    }
+                    const unsigned bal = __ballot_sync(0xffffffffu, take);
+                    if (bal) {
+                        int wbase = 0;
+                        if (wlane == 0) wbase = atomicAdd(qtail, __popc(bal));
+                        wbase = __shfl_sync(0xffffffffu, wbase, 0);
+                        if (take) {
+                            p.state[sbase + v] = 2;
+                            qnext[wbase + __popc(bal & ((1u << wlane) - 1))] = ((uint32_t)s << kVertexBits) | (uint32_t)v;
                         }
                     }
-                if (gtid == 0) p.ctl[s].thr = thr_new;
+                }
+                if (gtid == 0) {
+                    p.ctl[s].thr = thr_new;
+                    p.ctl[s].active[c_next] = 1;
+                }
             }
             grid.sync();
         }
@@ -246,6 +330,7 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
         for (int64_t i = gtid; i < (int64_t)B * n; i += gthreads)
             p.out_d32[i] = __double2float_rn(__longlong_as_double((long long)p.dist[i]));
         if (p.out_pred) {
+            const int64_t ggroup = gtid / kGroup, ngroups = gthreads / kGroup;
             for (int64_t item = ggroup; item < (int64_t)B * n; item += ngroups) {
                 const int s = (int)(item / n);
                 const int64_t v = item - (int64_t)s * n;
@@ -298,7 +383,7 @@ int coop_grid(int* grid_out) {
 }
 
 struct WsLayout {
-    int64_t dist, state, q0, q1, ctl, stats, total;
+    int64_t dist, state, q0, q1, ctl, gctl, stats, total;
 };
 WsLayout ws_layout(int64_t n, int slots, bool own_dist) {
     WsLayout w;
@@ -313,6 +398,8 @@ WsLayout ws_layout(int64_t n, int slots, bool own_dist) {
     off += align_up((int64_t)slots * n * 4, 256);
     w.ctl = off;
     off += align_up((int64_t)kMaxSlots * sizeof(SlotCtl), 256);
+    w.gctl = off;
+    off += 256;
     w.stats = off;
     off += 256;
     w.total = off;
@@ -335,7 +422,7 @@ GEOCB_API int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t 
                                double delta, int slots, void* workspace, int64_t workspace_bytes, float* out_d32,
                                int32_t* out_pred, int64_t* stats_host, void* stream) {
     ARG_CHECK(row_ptr && adj && sources && out_d32 && workspace);
-    ARG_CHECK(n > 0 && n < (1LL << 31) && S > 0 && slots >= 1 && slots <= kMaxSlots && delta > 0);
+    ARG_CHECK(n > 0 && n < (1LL << kVertexBits) && S > 0 && slots >= 1 && slots <= kMaxSlots && delta > 0);
     WsLayout w = ws_layout(n, slots, true);
     if (workspace_bytes < w.total) {
         geocb_set_error("sssp workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)w.total);
@@ -360,6 +447,7 @@ GEOCB_API int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t 
         p.queue[0] = (uint32_t*)(ws + w.q0);
         p.queue[1] = (uint32_t*)(ws + w.q1);
         p.ctl = (SlotCtl*)(ws + w.ctl);
+        p.gctl = (GlobalCtl*)(ws + w.gctl);
         p.stats = (unsigned long long*)(ws + w.stats);
         p.sources = sources + s0;
         p.out_d32 = out_d32 + (int64_t)s0 * n;
@@ -394,7 +482,7 @@ GEOCB_API int geocb_voronoi_insert(const int64_t* row_ptr, const void* adj, int6
                                    double delta, double* dmin64, float* dmin32, int32_t* label, void* workspace,
                                    int64_t workspace_bytes, void* stream) {
     ARG_CHECK(row_ptr && adj && dmin64 && dmin32 && label && workspace);
-    ARG_CHECK(n > 0 && n < (1LL << 31) && center >= 0 && center < n && delta > 0);
+    ARG_CHECK(n > 0 && n < (1LL << kVertexBits) && center >= 0 && center < n && delta > 0);
     WsLayout w = ws_layout(n, 1, false);
     if (workspace_bytes < w.total) {
         geocb_set_error("voronoi workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)w.total);
@@ -416,6 +504,7 @@ GEOCB_API int geocb_voronoi_insert(const int64_t* row_ptr, const void* adj, int6
     p.queue[0] = (uint32_t*)(ws + w.q0);
     p.queue[1] = (uint32_t*)(ws + w.q1);
     p.ctl = (SlotCtl*)(ws + w.ctl);
+    p.gctl = (GlobalCtl*)(ws + w.gctl);
     p.stats = nullptr;
     p.voronoi = 1;
     p.center = center;
