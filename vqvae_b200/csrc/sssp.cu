@@ -22,7 +22,11 @@ namespace {
 
 constexpr int kMaxSlots = 32;
 constexpr int kThreads = 256;
-constexpr int kGroup = 16;  // lanes cooperating on one vertex (16 x uint4 = 32 pairs per step)
+#ifndef GEOCB_GROUP
+#define GEOCB_GROUP 8
+#endif
+constexpr int kGroup = GEOCB_GROUP;  // lanes cooperating on one vertex (each lane: 2 x uint4 = 4 pairs per step)
+constexpr int kGroupsPerWarp = 32 / kGroup;
 
 struct SlotCtl {
     double thr;                  // current near/far threshold
@@ -33,7 +37,7 @@ struct SlotCtl {
 };
 struct GlobalCtl {
     int qcount[3];  // combined queue sizes: round r reads [r%3], fills [(r+1)%3], clears [(r+2)%3]
-    int pad;
+    int work[3];    // dynamic work cursor of phase A, same rotation
 };
 
 struct SsspParams {
@@ -87,30 +91,40 @@ __device__ __forceinline__ void stage_flush(uint32_t* wbuf, int* wcnt, uint32_t*
     __syncwarp();
 }
 
-__device__ __forceinline__ void relax_pair(uint32_t v, uint32_t wbits, double du, unsigned long long* dist_s,
-                                           int* state_s, double thr, uint32_t slot_tag, unsigned& active_mask,
-                                           uint32_t* wbuf, int* wcnt, uint32_t* qnext, int* qtail,
-                                           unsigned& n_improve) {
-    double cand = du + (double)__uint_as_float(wbits);
-    unsigned long long cb = (unsigned long long)__double_as_longlong(cand);
-    unsigned long long cur = ld_cg_u64(dist_s + v);
+__device__ __forceinline__ void red_min_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("red.global.min.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_max_s32(int* p, int v) {
+    asm volatile("red.global.max.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// The update half of a relaxation; the caller has already gathered `cur` = dist[v], so a lane keeps several
+// independent gathers in flight.  No returning atomic sits on the critical path: the distance is lowered with
+// a fire-and-forget red.min (a stale `cur` only costs a redundant red), and the queue flag is read first and
+// exchanged only when the vertex is not queued yet (about once per vertex per source).
+__device__ __forceinline__ void relax_update(uint32_t v, double cand, unsigned long long cur,
+                                             unsigned long long* dist_s, int* state_s, double thr, uint32_t slot_tag,
+                                             unsigned& active_mask, uint32_t* wbuf, int* wcnt, uint32_t* qnext,
+                                             int* qtail, unsigned& n_improve) {
+    const unsigned long long cb = (unsigned long long)__double_as_longlong(cand);
     if (cb < cur) {
-        unsigned long long old = atomicMin(dist_s + v, cb);
-        if (cb < old) {
-            ++n_improve;
-            if (cand < thr) {
-                if (atomicExch(state_s + v, 2) != 2) {
-                    active_mask |= 1u << (slot_tag >> kVertexBits);
-                    stage_push(slot_tag | v, wbuf, wcnt, qnext, qtail);
-                }
-            } else {
-                atomicMax(state_s + v, 1);
+        red_min_u64(dist_s + v, cb);
+        ++n_improve;
+        const int st = ld_cg_s32(state_s + v);
+        if (cand < thr) {
+            if (st != 2 && atomicExch(state_s + v, 2) != 2) {
+                active_mask |= 1u << (slot_tag >> kVertexBits);
+                stage_push(slot_tag | v, wbuf, wcnt, qnext, qtail);
             }
+        } else if (st == 0) {
+            red_max_s32(state_s + v, 1);
         }
     }
 }
 
-__global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
+#ifndef GEOCB_MINBLOCKS
+#define GEOCB_MINBLOCKS 4
+#endif
+__global__ void __launch_bounds__(kThreads, GEOCB_MINBLOCKS) sssp_kernel(SsspParams p) {
     cg::grid_group grid = cg::this_grid();
     const int64_t n = p.n;
     const int B = p.nslots;
@@ -134,6 +148,7 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
         p.gctl->qcount[0] = 0;
         p.gctl->qcount[1] = 0;
         p.gctl->qcount[2] = 0;
+        p.gctl->work[0] = p.gctl->work[1] = p.gctl->work[2] = 0;
     }
     grid.sync();
     if (gtid < B) {
@@ -157,10 +172,9 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
     unsigned n_relax = 0, n_improve = 0, n_rounds = 0, n_scans = 0;
     const int lane = threadIdx.x & (kGroup - 1);
     const int wlane = threadIdx.x & 31;
-    const int grp = (threadIdx.x >> 4) & 1;
+    const int grp = (threadIdx.x & 31) / kGroup;
     // the two 16-lane groups of a warp may hold different items: shuffles name only their own lanes
-    const unsigned gmask = 0xFFFFu << (threadIdx.x & 16);
-    const int64_t gwarp = gtid >> 5;
+    const unsigned gmask = (kGroup == 32 ? 0xFFFFFFFFu : ((1u << kGroup) - 1u)) << (grp * kGroup);
     const int64_t nwarps = gthreads >> 5;
     uint32_t* wbuf = s_stage[threadIdx.x >> 5];
     int* wcnt = &s_stage_n[threadIdx.x >> 5];
@@ -172,7 +186,10 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
             p.ctl[gtid].active[c_clear] = 0;
             p.ctl[gtid].far_min = D64_INF_BITS;
         }
-        if (gtid == 0) p.gctl->qcount[c_clear] = 0;
+        if (gtid == 0) {
+            p.gctl->qcount[c_clear] = 0;
+            p.gctl->work[c_clear] = 0;
+        }
         // ---- phase A0: un-queue every listed vertex (state 2 -> 0) before any distance is read, so that a
         //      later improvement of the same vertex re-queues it; the grid.sync replaces a per-item fence ----
         const int total = ld_cg_s32(&p.gctl->qcount[c_cur]);
@@ -188,44 +205,67 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
         int* qtail = &p.gctl->qcount[c_next];
         unsigned active_mask = 0;
         int chunk = 1;
-        while (chunk < kGroup && (int64_t)chunk * 2 * nwarps * 2 <= total) chunk <<= 1;
-        for (int64_t wbase = gwarp * 2 * chunk; wbase < total; wbase += nwarps * 2 * chunk) {
-            const int64_t my_item = wbase + (int64_t)grp * chunk + lane;
-            uint32_t entry = 0;
+        while (chunk < kGroup && (int64_t)chunk * 4 * nwarps * kGroupsPerWarp <= total) chunk <<= 1;
+        const int per_warp = kGroupsPerWarp * chunk;
+        const uint4 pad4 = make_uint4(0, F32_INF_BITS, 0, F32_INF_BITS);
+        for (;;) {
+            // warps grab work dynamically: rows differ in length and rounds end at a grid barrier
+            int wbase = 0;
+            if (wlane == 0) wbase = atomicAdd(&p.gctl->work[c_cur], per_warp);
+            wbase = __shfl_sync(0xffffffffu, wbase, 0);
+            if (wbase >= total) break;
+            const int my_item = wbase + grp * chunk + lane;
+            uint32_t entry = 0, beg = 0, end = 0;
             double du = 0.0, thr = 0.0;
-            int64_t beg = 0, end = 0;
             if (lane < chunk && my_item < total) {
                 entry = p.queue[par][my_item];
                 const int s = (int)(entry >> kVertexBits);
                 const uint32_t u = entry & kVertexMask;
                 du = __longlong_as_double((long long)ld_cg_u64(p.dist + (int64_t)s * n + u));
                 thr = __longlong_as_double((long long)ld_cg_u64((const unsigned long long*)&p.ctl[s].thr));
-                beg = __ldg(p.row_ptr + u) >> 1;
-                end = __ldg(p.row_ptr + u + 1) >> 1;
+                beg = (uint32_t)(__ldg(p.row_ptr + u) >> 1);
+                end = (uint32_t)(__ldg(p.row_ptr + u + 1) >> 1);
             }
+            // software pipeline: the pair loads of item j+1 are issued before item j's gathers are consumed
+            uint32_t nbeg = __shfl_sync(gmask, beg, 0, kGroup), nend = __shfl_sync(gmask, end, 0, kGroup);
+            uint4 n0 = pad4, n1 = pad4;
+            if (nbeg + lane < nend) n0 = ld_stream_v4(p.adj4 + nbeg + lane);
+            if (nbeg + lane + kGroup < nend) n1 = ld_stream_v4(p.adj4 + nbeg + lane + kGroup);
             for (int j = 0; j < chunk; ++j) {
                 const uint32_t e_j = __shfl_sync(gmask, entry, j, kGroup);
                 const double du_j = __shfl_sync(gmask, du, j, kGroup);
                 const double thr_j = __shfl_sync(gmask, thr, j, kGroup);
-                const int64_t beg_j = __shfl_sync(gmask, beg, j, kGroup);
-                const int64_t end_j = __shfl_sync(gmask, end, j, kGroup);
+                const uint32_t beg_j = nbeg, end_j = nend;
+                uint4 e0 = n0, e1 = n1;
+                if (j + 1 < chunk) {
+                    nbeg = __shfl_sync(gmask, beg, j + 1, kGroup);
+                    nend = __shfl_sync(gmask, end, j + 1, kGroup);
+                    n0 = pad4;
+                    n1 = pad4;
+                    if (nbeg + lane < nend) n0 = ld_stream_v4(p.adj4 + nbeg + lane);
+                    if (nbeg + lane + kGroup < nend) n1 = ld_stream_v4(p.adj4 + nbeg + lane + kGroup);
+                }
                 const int64_t sbase = (int64_t)(e_j >> kVertexBits) * n;
                 unsigned long long* dist_s = p.dist + sbase;
                 int* state_s = p.state + sbase;
                 const uint32_t tag = e_j & ~kVertexMask;
-                for (int64_t i = beg_j + lane; i < end_j; i += 2 * kGroup) {
-                    // two 128-bit pair loads in flight per lane, then four distance gathers, then the updates
-                    const bool second = i + kGroup < end_j;
-                    const uint4 e0 = ld_stream_v4(p.adj4 + i);
-                    uint4 e1 = make_uint4(0, F32_INF_BITS, 0, F32_INF_BITS);
-                    if (second) e1 = ld_stream_v4(p.adj4 + i + kGroup);
-                    n_relax += second ? 4 : 2;
-                    relax_pair(e0.x, e0.y, du_j, dist_s, state_s, thr_j, tag, active_mask, wbuf, wcnt, qnext, qtail, n_improve);
-                    relax_pair(e0.z, e0.w, du_j, dist_s, state_s, thr_j, tag, active_mask, wbuf, wcnt, qnext, qtail, n_improve);
-                    if (second) {
-                        relax_pair(e1.x, e1.y, du_j, dist_s, state_s, thr_j, tag, active_mask, wbuf, wcnt, qnext, qtail, n_improve);
-                        relax_pair(e1.z, e1.w, du_j, dist_s, state_s, thr_j, tag, active_mask, wbuf, wcnt, qnext, qtail, n_improve);
-                    }
+                for (uint32_t i = beg_j + lane;;) {
+                    // four independent distance gathers in flight, then the (rare) updates
+                    const unsigned long long d0 = ld_cg_u64(dist_s + e0.x), d1 = ld_cg_u64(dist_s + e0.z);
+                    const unsigned long long d2 = ld_cg_u64(dist_s + e1.x), d3 = ld_cg_u64(dist_s + e1.z);
+                    n_relax += (i < end_j ? 2 : 0) + (i + kGroup < end_j ? 2 : 0);
+                    relax_update(e0.x, du_j + (double)__uint_as_float(e0.y), d0, dist_s, state_s, thr_j, tag, active_mask,
+                                 wbuf, wcnt, qnext, qtail, n_improve);
+                    relax_update(e0.z, du_j + (double)__uint_as_float(e0.w), d1, dist_s, state_s, thr_j, tag, active_mask,
+                                 wbuf, wcnt, qnext, qtail, n_improve);
+                    relax_update(e1.x, du_j + (double)__uint_as_float(e1.y), d2, dist_s, state_s, thr_j, tag, active_mask,
+                                 wbuf, wcnt, qnext, qtail, n_improve);
+                    relax_update(e1.z, du_j + (double)__uint_as_float(e1.w), d3, dist_s, state_s, thr_j, tag, active_mask,
+                                 wbuf, wcnt, qnext, qtail, n_improve);
+                    i += 2 * kGroup;
+                    if (i >= end_j) break;  // rows longer than 4*kGroup pairs take further trips
+                    e0 = ld_stream_v4(p.adj4 + i);
+                    e1 = i + kGroup < end_j ? ld_stream_v4(p.adj4 + i + kGroup) : pad4;
                 }
                 stage_flush(wbuf, wcnt, qnext, qtail, kStage / 2);
             }
@@ -254,11 +294,17 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
                 if (!s_need[s]) continue;
                 const int64_t sbase = (int64_t)s * n;
                 unsigned long long m = D64_INF_BITS;
-                for (int64_t v = gtid; v < n; v += gthreads)
-                    if (ld_cg_s32(p.state + sbase + v) == 1) {
-                        unsigned long long d = ld_cg_u64(p.dist + sbase + v);
-                        m = d < m ? d : m;
-                    }
+                for (int64_t v = gtid; v < n; v += 4 * gthreads) {
+                    int st[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) st[k] = v + k * gthreads < n ? ld_cg_s32(p.state + sbase + v + k * gthreads) : 0;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (st[k] == 1) {
+                            unsigned long long d = ld_cg_u64(p.dist + sbase + v + k * gthreads);
+                            m = d < m ? d : m;
+                        }
+                }
                 for (int o = 16; o; o >>= 1) {
                     unsigned long long t = __shfl_xor_sync(0xffffffffu, m, o);
                     m = t < m ? t : m;
@@ -283,20 +329,28 @@ __global__ void __launch_bounds__(kThreads) sssp_kernel(SsspParams p) {
                 const double thr_new = __longlong_as_double((long long)fm) + p.delta;
                 const int64_t sbase = (int64_t)s * n;
                 const int64_t n_round = (n + 31) & ~(int64_t)31;
-                for (int64_t v = gtid; v < n_round; v += gthreads) {
-                    bool take = false;
-                    if (v < n && ld_cg_s32(p.state + sbase + v) == 1) {
-                        double d = __longlong_as_double((long long)ld_cg_u64(p.dist + sbase + v));
-                        take = d < thr_new;
-                    }
-                    const unsigned bal = __ballot_sync(0xffffffffu, take);
-                    if (bal) {
-                        int wbase = 0;
-                        if (wlane == 0) wbase = atomicAdd(qtail, __popc(bal));
-                        wbase = __shfl_sync(0xffffffffu, wbase, 0);
-                        if (take) {
-                            p.state[sbase + v] = 2;
-                            qnext[wbase + __popc(bal & ((1u << wlane) - 1))] = ((uint32_t)s << kVertexBits) | (uint32_t)v;
+                for (int64_t v0 = gtid; v0 < n_round; v0 += 4 * gthreads) {
+                    int st[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) st[k] = v0 + k * gthreads < n ? ld_cg_s32(p.state + sbase + v0 + k * gthreads) : 0;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int64_t v = v0 + k * gthreads;
+                        if (v - wlane >= n_round) break;  // warp-uniform
+                        bool take = false;
+                        if (st[k] == 1) {
+                            double d = __longlong_as_double((long long)ld_cg_u64(p.dist + sbase + v));
+                            take = d < thr_new;
+                        }
+                        const unsigned bal = __ballot_sync(0xffffffffu, take);
+                        if (bal) {
+                            int wbase = 0;
+                            if (wlane == 0) wbase = atomicAdd(qtail, __popc(bal));
+                            wbase = __shfl_sync(0xffffffffu, wbase, 0);
+                            if (take) {
+                                p.state[sbase + v] = 2;
+                                qnext[wbase + __popc(bal & ((1u << wlane) - 1))] = ((uint32_t)s << kVertexBits) | (uint32_t)v;
+                            }
                         }
                     }
                 }

@@ -141,21 +141,62 @@ def _gn_pair(m, x, t):
     return xh, th
 
 
-def _forward_mode(layers, z, dz, groups):
-    """sigmoid(decoder(z)) tangent for rows z (R,C) with direction dz; returns (R,P)."""
-    x, t = z[:, :, None, None], dz[:, :, None, None]
+def _unrolled_ops(layers, latent_dim):
+    """Decoder on a 1x1 latent grid as dense operators: every conv / transposed conv becomes the matrix of
+    the linear map it applies to its (C,H,W) input (obtained by pushing an identity basis through the layer
+    itself, so each entry is exactly one kernel weight or 0), which turns the stack into fp32 GEMMs."""
+    ops, shape = [], (latent_dim, 1, 1)
     for m in layers:
         if isinstance(m, (nn.Conv2d, nn.ConvTranspose2d)):
-            x, t = _conv_pair(m, x, t)
+            k = shape[0] * shape[1] * shape[2]
+            eye = torch.eye(k, device=m.weight.device, dtype=m.weight.dtype).view(k, *shape)
+            if isinstance(m, nn.Conv2d):
+                out = F.conv2d(eye, m.weight, None, m.stride, m.padding, m.dilation, m.groups)
+            else:
+                out = F.conv_transpose2d(eye, m.weight, None, m.stride, m.padding, m.output_padding, m.groups, m.dilation)
+            oshape = tuple(out.shape[1:])
+            bias = None if m.bias is None else m.bias.view(-1, 1, 1).expand(oshape).reshape(-1).contiguous()
+            A = out.reshape(k, -1).contiguous()
+            if ops and ops[-1][0] == "lin":
+                # two linear maps in a row (conv_in -> first ConvT): compose once, in fp64, round once
+                _, A0, b0, _ = ops.pop()
+                A64 = A0.double() @ A.double()
+                if b0 is not None:
+                    b64 = b0.double() @ A.double() + (0 if bias is None else bias.double())
+                    bias = b64.float()
+                A = A64.float().contiguous()
+            ops.append(("lin", A, bias, oshape))
+            shape = oshape
         elif isinstance(m, nn.BatchNorm2d):
-            x, t = _bn_pair(m, x, t, groups)
+            ops.append(("bn", m, shape))
         elif isinstance(m, nn.GroupNorm):
-            x, t = _gn_pair(m, x, t)
+            ops.append(("gn", m, shape))
         elif isinstance(m, nn.ReLU):
+            ops.append(("relu",))
+    return ops
+
+
+def _forward_mode(ops, z, dz, groups):
+    """Tangent of sigmoid(decoder(z)) along dz for rows z (R,C); returns (R,P)."""
+    x, t = z, dz
+    n = z.shape[0]
+    for op in ops:
+        if op[0] == "lin":
+            y = torch.cat([x, t], 0) @ op[1]  # primal and tangent share one GEMM
+            x, t = y[:n], y[n:]
+            if op[2] is not None:
+                x = x + op[2]
+        elif op[0] == "bn":
+            x4, t4 = _bn_pair(op[1], x.view(n, *op[2]), t.view(n, *op[2]), groups)
+            x, t = x4.reshape(n, -1), t4.reshape(n, -1)
+        elif op[0] == "gn":
+            x4, t4 = _gn_pair(op[1], x.view(n, *op[2]), t.view(n, *op[2]))
+            x, t = x4.reshape(n, -1), t4.reshape(n, -1)
+        else:
             t = t * (x > 0)
             x = torch.relu(x)
     s = torch.sigmoid(x)  # always applied (:29)
-    return (s * (1 - s) * t).reshape(z.shape[0], -1)
+    return s * (1 - s) * t
 
 
 @torch.no_grad()
@@ -173,6 +214,9 @@ def edge_lengths_device(decoder, z_flat, ei, ej, batch_size=512, pos_ij=None, po
     dev = z_flat.device
     out = torch.empty(max(e_hi - e_lo, 0), dtype=torch.float32, device=dev)
     layers = None if _is_flat_decoder(decoder) else _flatten_layers(decoder)
+    if layers is not None:
+        with _strict_fp32():
+            layers = _unrolled_ops(layers, z_flat.shape[1])
     with _strict_fp32():
         lo = e_lo
         while lo < e_hi:
