@@ -109,12 +109,15 @@ int64_t geocb_sssp_workspace_bytes(int64_t n, int slots);
  * (geo_shortest_paths.py:36-49).  S independent single-source problems solved by a
  * near-far (delta-stepping) frontier relaxation that accumulates path sums in fp64
  * exactly like scipy (monotone rounded addition => same fixed point as Dijkstra),
- * `slots` sources in flight at once; results rounded to f32 at the end.
+ * `slots` (1..32) sources in flight per cooperative launch; results rounded to f32 at the end.
+ * Per relaxation the kernel gathers only a float32 upper bound of dist[v] (exact filter),
+ * frontiers are bitmaps swept in vertex order (see csrc/sssp.cu).
  *   out_d32[S,n] f32 (+inf unreachable); out_pred[S,n] int32 or NULL
  *   (predecessor = lowest-index neighbour u with fl(d[u]+w)==d[v]; -9999 for the
  *   source and unreachable vertices, scipy's convention).
- * delta <= 0 -> weight_mean (mean edge weight).  Syncs.  stats_host (nullable):
- * int64[4] = {edge relaxations, rounds, threshold scans, improvements}. */
+ * delta > 0 (callers pass the mean edge weight).  Syncs.  stats_host (nullable):
+ * int64[4] = {edge relaxations, rounds, threshold scans, improvements}.
+ * Returns GEOCB_ERR_OVERFLOW if the kernel hit its round limit (8n+4096) without converging. */
 int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t n, const int32_t* sources, int S,
                      double delta, int slots, void* workspace, int64_t workspace_bytes, float* out_d32,
                      int32_t* out_pred, int64_t* stats_host, void* stream);
@@ -127,9 +130,11 @@ int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t n, const i
  * smaller (exact in fp64 by monotonicity of rounded addition), then
  *   dmin32[v] = f32(dmin64[v]);  label[v] = k  iff f32 value strictly decreased
  * which is the reference's  argmin over k of float32(D[k,v]) with lowest-k ties.
- * geocb_voronoi_init sets dmin64=+inf, dmin32=+inf, label=-1. */
+ * geocb_voronoi_init sets dmin64=+inf, dmin32=+inf, label=-1 and initialises the workspace, which must then be
+ * passed unchanged to every geocb_voronoi_insert of that state (it holds the kernel's per-vertex bookkeeping). */
 int64_t geocb_voronoi_workspace_bytes(int64_t n);
-int geocb_voronoi_init(int64_t n, double* dmin64, float* dmin32, int32_t* label, void* stream);
+int geocb_voronoi_init(int64_t n, double* dmin64, float* dmin32, int32_t* label, void* workspace,
+                       int64_t workspace_bytes, void* stream);
 int geocb_voronoi_insert(const int64_t* row_ptr, const void* adj, int64_t n, int32_t center, int32_t code,
                          double delta, double* dmin64, float* dmin32, int32_t* label, void* workspace,
                          int64_t workspace_bytes, void* stream);

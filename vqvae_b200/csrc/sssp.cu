@@ -3,55 +3,76 @@
 // Replaces scipy.sparse.csgraph.dijkstra as called by the reference at
 // src/geo/geo_shortest_paths.py:36-49 (and through it kmeans_optimized.py:42,97,125).
 //
-// Algorithm: near-far (delta-stepping) frontier relaxation, push style.
-//   dist[v] is an fp64 kept as its uint64 bit pattern (non-negative doubles order as
-//   unsigned integers) so `atomicMin(u64)` is an exact fp64 min.  A relaxation computes
-//   fl64(dist[u] + (double)w) -- the same rounded addition, in the same source->target
-//   order, scipy's Dijkstra performs -- and because rounded addition is monotone the
+// Algorithm: near-far (delta-stepping) frontier relaxation, push style, fp64-exact.
+//   dist[v] is an fp64 kept as its uint64 bit pattern (non-negative doubles order as unsigned integers) so a
+//   u64 min IS an fp64 min.  A relaxation computes fl64(dist[u] + (double)w) -- the same rounded addition, in
+//   the same source->target order, scipy's Dijkstra performs -- and because rounded addition is monotone the
 //   label-correcting fixed point is bit-identical to Dijkstra's result.
-//   One persistent cooperative kernel runs all rounds of `slots` concurrent sources:
-//     phase A  every queued (slot,u): 16 lanes stream u's (col,w) pairs with 128-bit loads,
-//              gather dist[v] from L2, atomicMin the improvements and queue v
-//              (near: cand < thr[slot]) or mark it dirty (far);
-//     phase B  for slots whose near queue ran dry: thr = min(dirty dist)+delta, queue dirty<thr.
-// HBM model: 8 B per relaxation streamed (the pair) + 8 B dist gather (L2 resident
-// when slots*n*8 B fits) ; algorithmic bytes = 16*(nnz+n) per source.
+//
+// What the hardware allows (tools/ubench/gather.cu, B200): 275 G random 4/8-byte gathers/s when the gathered
+// array stays in L2 (<= ~60 MB), ~50 G/s when it comes from DRAM.  One relaxation = one gather of dist[v], so
+// the design keeps the gathered array small and everything else sequential or fire-and-forget:
+//   ub[v]    float32 upper bound, ub = round_up_f32(dist) -- the ONLY array gathered per relaxation (4 B/vertex/
+//            source; L2 evict_last hint -- a persisting-L2 carve-out made things worse and is not used).
+//            cand cannot improve v  <=>  round_down_f32(cand) >= ub[v]  (exact);
+//            otherwise red.min.u64 dist[v], red.min.u32 ub[v] and a frontier bit are fired without waiting.
+//   inq[2]   frontier bitmaps (1 bit per vertex and source, double-buffered by round parity): improvements
+//            below the slot threshold set inq[next]; a round sweeps inq[cur] word by word, so popped vertices
+//            are consecutive -- dist/proc/row_ptr reads coalesce and adjacency rows stream sequentially.
+//   dirty    bitmap of vertices improved to a value >= threshold ("far"); when a slot's frontier runs dry the
+//            threshold rises by delta and dirty vertices with ub below it move to the frontier.
+//   proc[v]  distance v's row was last relaxed with; a popped vertex is relaxed only if dist[v] < proc[v], which
+//            drops the (rare) spurious frontier bits of the float filter and stale far marks exactly.
+//   One persistent cooperative kernel runs all rounds of `slots` concurrent sources; rounds are separated by
+//   grid.sync.  A warp flattens the rows of its <=32 popped vertices into one edge range and walks it 128 edges
+//   per trip, the next trip's edge loads issued before this trip's gathers are consumed.
+// HBM model: 8 B edge pair + 8 B distance per relaxation = 16*(nnz+n) algorithmic bytes per source.
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace {
 
 constexpr int kMaxSlots = 32;
-constexpr int kThreads = 256;
-#ifndef GEOCB_GROUP
-#define GEOCB_GROUP 8
+#ifndef GEOCB_SSSP_THREADS
+#define GEOCB_SSSP_THREADS 256
 #endif
-constexpr int kGroup = GEOCB_GROUP;  // lanes cooperating on one vertex (each lane: 2 x uint4 = 4 pairs per step)
-constexpr int kGroupsPerWarp = 32 / kGroup;
+#ifndef GEOCB_SSSP_MINBLOCKS
+#define GEOCB_SSSP_MINBLOCKS 3
+#endif
+constexpr int kThreads = GEOCB_SSSP_THREADS;
+constexpr int kWarps = kThreads / 32;
+#ifndef GEOCB_SSSP_PER
+#define GEOCB_SSSP_PER 4
+#endif
+constexpr int kPer = GEOCB_SSSP_PER;  // edges (= independent ub gathers in flight) per lane per trip: 4 or 8
+constexpr int kTile = 32 * kPer;      // flat edges per warp trip
+typedef unsigned long long u64;
 
 struct SlotCtl {
-    double thr;                  // current near/far threshold
-    unsigned long long far_min;  // min dist bits over dirty vertices (phase B1)
-    int active[3];               // "something was queued for this slot", rotating like GlobalCtl::qcount
-    int done;
-    int pad[2];
-};
-struct GlobalCtl {
-    int qcount[3];  // combined queue sizes: round r reads [r%3], fills [(r+1)%3], clears [(r+2)%3]
-    int work[3];    // dynamic work cursor of phase A, same rotation
+    double thr2[2];         // near/far threshold, double-buffered by the slot's scan count (block-local epoch)
+    uint32_t scan_min[3];   // min ub (f32 bits) over vertices left dirty by the scan of round r (index r%3)
+    int scan_pushed[3];
+    int active[3];          // "the slot has frontier bits for the next round", index (r+1)%3 written in round r
+    int pad;
+    u64 work[3];            // (slot 0 only) phase-A grab cursor: round r uses [r%3], clears [(r+2)%3]
 };
 
 struct SsspParams {
     const int64_t* row_ptr;
-    const uint4* adj4;
+    const uint2* adj;
     int64_t n;
+    int64_t nwords;  // bitmap words per slot (multiple of 32)
     int nslots;
+    int max_rounds;  // safety net: a kernel that cannot converge must not hang the device
+    int* failed;     // device flag, set when max_rounds was hit
     double delta;
-    unsigned long long* dist;  // [nslots][n]
-    int* state;                // [nslots][n]  0 clean, 1 dirty (far), 2 queued (near)
-    uint32_t* queue[2];        // combined work lists, entries (slot << 27) | vertex, capacity nslots*n each
-    SlotCtl* ctl;              // [nslots]
-    GlobalCtl* gctl;
-    unsigned long long* stats; // [4]
+    u64* dist;         // [nslots][n] fp64 bits
+    u64* proc;         // [nslots][n] fp64 bits
+    uint32_t* ub;      // [nslots][n] f32 bits
+    uint32_t* inq[2];  // [nslots][nwords]
+    uint32_t* dirty;   // [nslots][nwords]
+    SlotCtl* ctl;      // [nslots]
+    u64* stats;        // [4] counters + round trace; nullable
     // full-SSSP mode
     const int32_t* sources;  // [nslots]
     float* out_d32;          // [nslots][n]
@@ -63,106 +84,147 @@ struct SsspParams {
     int32_t* label;
 };
 
-constexpr int kVertexBits = 27;
-constexpr uint32_t kVertexMask = (1u << kVertexBits) - 1;
-constexpr int kStage = 128;  // per-warp staging entries before one aggregated global atomicAdd
-
-// queue push through the warp's shared-memory staging buffer (same-address global atomics on the queue
-// tail serialise in L2: ~1 cycle each, which capped the first version at 5 % of roofline)
-__device__ __forceinline__ void stage_push(uint32_t entry, uint32_t* wbuf, int* wcnt, uint32_t* qnext, int* qtail) {
-    const int pos = atomicAdd(wcnt, 1);
-    if (pos < kStage) wbuf[pos] = entry;
-    else qnext[atomicAdd(qtail, 1)] = entry;  // staging full (rare): straight to the global list
+// ---- L2 residency control: the gathered ub array stays (evict_last), edge pairs stream through (evict_first) ----
+__device__ __forceinline__ uint64_t policy_evict_last() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
 }
-// warp-synchronous flush; every lane of the warp must call it
-__device__ __forceinline__ void stage_flush(uint32_t* wbuf, int* wcnt, uint32_t* qnext, int* qtail, int min_fill) {
-    __syncwarp();
-    int cnt = *(volatile int*)wcnt;
-    if (cnt >= min_fill && cnt > 0) {
-        cnt = cnt < kStage ? cnt : kStage;
-        const int wl = threadIdx.x & 31;
-        int base = 0;
-        if (wl == 0) base = atomicAdd(qtail, cnt);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        for (int i = wl; i < cnt; i += 32) qnext[base + i] = wbuf[i];
-        __syncwarp();
-        if (wl == 0) *(volatile int*)wcnt = 0;
-    }
-    __syncwarp();
+__device__ __forceinline__ uint64_t policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
 }
-
-__device__ __forceinline__ void red_min_u64(unsigned long long* p, unsigned long long v) {
+__device__ __forceinline__ uint32_t ld_ub(const uint32_t* p, uint64_t pol) {
+    uint32_t v;
+#ifdef GEOCB_SSSP_NOHINT_UB
+    asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(v) : "l"(p));
+#else
+    asm volatile("ld.global.cg.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+#endif
+    return v;
+}
+__device__ __forceinline__ uint2 ld_edge(const uint2* p, uint64_t pol) {
+    uint2 v;
+#ifdef GEOCB_SSSP_NOHINT_EDGE
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+#else
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u32 {%0,%1}, [%2], %3;"
+                 : "=r"(v.x), "=r"(v.y)
+                 : "l"(p), "l"(pol));
+#endif
+    return v;
+}
+__device__ __forceinline__ void red_min_u64(u64* p, u64 v) {
     asm volatile("red.global.min.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ void red_max_s32(int* p, int v) {
-    asm volatile("red.global.max.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ void red_min_u32(uint32_t* p, uint32_t v, uint64_t pol) {
+#ifdef GEOCB_SSSP_NOHINT_UB
+    asm volatile("red.global.min.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+#else
+    asm volatile("red.global.min.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(p), "r"(v), "l"(pol) : "memory");
+#endif
 }
-// The update half of a relaxation; the caller has already gathered `cur` = dist[v], so a lane keeps several
-// independent gathers in flight.  No returning atomic sits on the critical path: the distance is lowered with
-// a fire-and-forget red.min (a stale `cur` only costs a redundant red), and the queue flag is read first and
-// exchanged only when the vertex is not queued yet (about once per vertex per source).
-__device__ __forceinline__ void relax_update(uint32_t v, double cand, unsigned long long cur,
-                                             unsigned long long* dist_s, int* state_s, double thr, uint32_t slot_tag,
-                                             unsigned& active_mask, uint32_t* wbuf, int* wcnt, uint32_t* qnext,
-                                             int* qtail, unsigned& n_improve) {
-    const unsigned long long cb = (unsigned long long)__double_as_longlong(cand);
-    if (cb < cur) {
-        red_min_u64(dist_s + v, cb);
-        ++n_improve;
-        const int st = ld_cg_s32(state_s + v);
-        if (cand < thr) {
-            if (st != 2 && atomicExch(state_s + v, 2) != 2) {
-                active_mask |= 1u << (slot_tag >> kVertexBits);
-                stage_push(slot_tag | v, wbuf, wcnt, qnext, qtail);
-            }
-        } else if (st == 0) {
-            red_max_s32(state_s + v, 1);
-        }
-    }
+__device__ __forceinline__ void red_or_u32(uint32_t* p, uint32_t v) {
+    asm volatile("red.global.or.b32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_and_u32(uint32_t* p, uint32_t v) {
+    asm volatile("red.global.and.b32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_cg_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ double ld_cg_f64(const double* p) {
+    return __longlong_as_double((long long)ld_cg_u64((const u64*)p));
 }
 
-#ifndef GEOCB_MINBLOCKS
-#define GEOCB_MINBLOCKS 4
-#endif
-__global__ void __launch_bounds__(kThreads, GEOCB_MINBLOCKS) sssp_kernel(SsspParams p) {
+// owner lane (+1) of each of this lane's kPer flat positions tile+kPer*lane+k, given each lane's item [start,start+len)
+__device__ __forceinline__ void locate(uint32_t tile, uint32_t start, uint32_t len, uint32_t* own32, int wl, int j[kPer]) {
+    constexpr int kW = kPer / 4;  // marker words per lane (one byte per flat position)
+    __syncwarp();
+#pragma unroll
+    for (int w = 0; w < kW; ++w) own32[wl * kW + w] = 0;
+    __syncwarp();
+    if (len > 0 && start >= tile && start - tile < kTile) ((uint8_t*)own32)[start - tile] = (uint8_t)(wl + 1);
+    __syncwarp();
+    const unsigned before = __ballot_sync(0xffffffffu, len > 0 && start < tile);
+    const int carry = before ? 32 - __clz(before) : 0;
+    int m[kPer];
+    int run = 0;
+#pragma unroll
+    for (int w = 0; w < kW; ++w) {
+        const uint32_t ow = own32[wl * kW + w];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            run = max(run, (int)((ow >> (8 * b)) & 255u));
+            m[w * 4 + b] = run;
+        }
+    }
+    int sc = run;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, sc, o);
+        if (wl >= o) sc = max(sc, t);
+    }
+    int ex = __shfl_up_sync(0xffffffffu, sc, 1);
+    if (wl == 0) ex = 0;
+    ex = max(ex, carry);
+#pragma unroll
+    for (int i = 0; i < kPer; ++i) j[i] = max(max(ex, m[i]) - 1, 0);
+}
+
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+__global__ void __launch_bounds__(kThreads, GEOCB_SSSP_MINBLOCKS) sssp_kernel(SsspParams p) {
     cg::grid_group grid = cg::this_grid();
     const int64_t n = p.n;
+    const int64_t nwords = p.nwords;
     const int B = p.nslots;
     const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
-    __shared__ int s_need[kMaxSlots];
+    const int64_t gwarp = gtid >> 5, nwarps = gthreads >> 5;
+    const int wlane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    __shared__ double s_thr[kMaxSlots], s_hint[kMaxSlots];
+    __shared__ int s_epoch[kMaxSlots], s_done[kMaxSlots], s_need[kMaxSlots];
     __shared__ int s_flag, s_alldone;
-    __shared__ unsigned long long s_red[kThreads / 32];
-    __shared__ uint32_t s_stage[kThreads / 32][kStage];
-    __shared__ int s_stage_n[kThreads / 32];
+    __shared__ uint32_t s_own[kWarps][kTile / 4];
+    uint32_t* own32 = s_own[wib];
+    const uint64_t pol_keep = policy_evict_last();
+    const uint64_t pol_stream = policy_evict_first();
 
     // ---- init ----
     if (!p.voronoi) {
         for (int64_t i = gtid; i < (int64_t)B * n; i += gthreads) {
             p.dist[i] = D64_INF_BITS;
-            p.state[i] = 0;
+            p.proc[i] = D64_INF_BITS;
+            p.ub[i] = F32_INF_BITS;
+        }
+        for (int64_t i = gtid; i < (int64_t)B * nwords; i += gthreads) {
+            p.inq[0][i] = 0;
+            p.inq[1][i] = 0;
+            p.dirty[i] = 0;
         }
     }
-    if (threadIdx.x < kThreads / 32) s_stage_n[threadIdx.x] = 0;
-    if (gtid == 0) {
-        p.gctl->qcount[0] = 0;
-        p.gctl->qcount[1] = 0;
-        p.gctl->qcount[2] = 0;
-        p.gctl->work[0] = p.gctl->work[1] = p.gctl->work[2] = 0;
+    if (threadIdx.x < kMaxSlots) {
+        s_epoch[threadIdx.x] = 0;
+        s_done[threadIdx.x] = 0;
+        s_hint[threadIdx.x] = 0.0;
     }
     grid.sync();
     if (gtid < B) {
-        int s = (int)gtid;
-        int src = p.voronoi ? p.center : p.sources[s];
+        const int s = (int)gtid;
+        const int src = p.voronoi ? p.center : p.sources[s];
         SlotCtl c;
-        c.thr = p.delta;
-        c.far_min = D64_INF_BITS;
-        c.active[0] = c.active[1] = c.active[2] = 0;
-        c.done = 0;
-        unsigned long long old = atomicMin(p.dist + (int64_t)s * n + src, 0ULL);
+        c.thr2[0] = c.thr2[1] = p.delta;
+        for (int i = 0; i < 3; ++i) c.scan_min[i] = F32_INF_BITS, c.scan_pushed[i] = 0, c.active[i] = 0;
+        c.pad = 0;
+        c.work[0] = c.work[1] = c.work[2] = 0;
+        const u64 old = atomicMin(p.dist + (int64_t)s * n + src, 0ULL);
         if (old != 0ULL) {  // (voronoi: re-inserting an existing centre changes nothing)
-            p.state[(int64_t)s * n + src] = 2;
-            p.queue[0][atomicAdd(&p.gctl->qcount[0], 1)] = ((uint32_t)s << kVertexBits) | (uint32_t)src;
+            p.ub[(int64_t)s * n + src] = 0u;
+            atomicOr(p.inq[0] + (int64_t)s * nwords + (src >> 5), 1u << (src & 31));
             c.active[0] = 1;
         }
         p.ctl[s] = c;
@@ -170,203 +232,257 @@ __global__ void __launch_bounds__(kThreads, GEOCB_MINBLOCKS) sssp_kernel(SsspPar
     grid.sync();
 
     unsigned n_relax = 0, n_improve = 0, n_rounds = 0, n_scans = 0;
-    const int lane = threadIdx.x & (kGroup - 1);
-    const int wlane = threadIdx.x & 31;
-    const int grp = (threadIdx.x & 31) / kGroup;
-    // the two 16-lane groups of a warp may hold different items: shuffles name only their own lanes
-    const unsigned gmask = (kGroup == 32 ? 0xFFFFFFFFu : ((1u << kGroup) - 1u)) << (grp * kGroup);
-    const int64_t nwarps = gthreads >> 5;
-    uint32_t* wbuf = s_stage[threadIdx.x >> 5];
-    int* wcnt = &s_stage_n[threadIdx.x >> 5];
+    const uint2 pad_edge = make_uint2(0u, F32_INF_BITS);
+    const int64_t ngroups = nwords / 32;  // grabs per slot
 
     for (int round = 0;; ++round) {
-        const int par = round & 1;  // queue buffer parity
         const int c_cur = round % 3, c_next = (round + 1) % 3, c_clear = (round + 2) % 3;
-        if (gtid < B) {  // safe: all of these were last touched before the previous grid.sync
-            p.ctl[gtid].active[c_clear] = 0;
-            p.ctl[gtid].far_min = D64_INF_BITS;
+        uint32_t* inq_cur = (round & 1) ? p.inq[1] : p.inq[0];
+        uint32_t* inq_next = (round & 1) ? p.inq[0] : p.inq[1];
+        if (gtid < B) p.ctl[gtid].active[c_clear] = 0;  // last read before the previous round's grid.sync
+        if (gtid == 0) p.ctl[0].work[c_clear] = 0;     // last used before the previous round's grid.sync
+        if (threadIdx.x < B) s_thr[threadIdx.x] = ld_cg_f64(&p.ctl[threadIdx.x].thr2[s_epoch[threadIdx.x] & 1]);
+        __syncthreads();
+        if (p.stats && gtid == 0 && round < 120) {  // round trace for tools/prof_sssp.py
+            u64 t;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+            p.stats[8 + 2 * round] = t;
         }
-        if (gtid == 0) {
-            p.gctl->qcount[c_clear] = 0;
-            p.gctl->work[c_clear] = 0;
-        }
-        // ---- phase A0: un-queue every listed vertex (state 2 -> 0) before any distance is read, so that a
-        //      later improvement of the same vertex re-queues it; the grid.sync replaces a per-item fence ----
-        const int total = ld_cg_s32(&p.gctl->qcount[c_cur]);
-        for (int64_t i = gtid; i < total; i += gthreads) {
-            const uint32_t entry = p.queue[par][i];
-            p.state[(int64_t)(entry >> kVertexBits) * n + (entry & kVertexMask)] = 0;
-        }
-        grid.sync();
-        // ---- phase A: relax every queued (slot, vertex).  Each 16-lane group prefetches a chunk of `chunk`
-        //      items (entry, dist[u], row bounds, threshold: independent loads, one per lane) and then walks
-        //      them; the trip count is uniform per warp so the staging flush can be warp-synchronous ----
-        uint32_t* qnext = p.queue[par ^ 1];
-        int* qtail = &p.gctl->qcount[c_next];
-        unsigned active_mask = 0;
-        int chunk = 1;
-        while (chunk < kGroup && (int64_t)chunk * 4 * nwarps * kGroupsPerWarp <= total) chunk <<= 1;
-        const int per_warp = kGroupsPerWarp * chunk;
-        const uint4 pad4 = make_uint4(0, F32_INF_BITS, 0, F32_INF_BITS);
-        for (;;) {
-            // warps grab work dynamically: rows differ in length and rounds end at a grid barrier
-            int wbase = 0;
-            if (wlane == 0) wbase = atomicAdd(&p.gctl->work[c_cur], per_warp);
-            wbase = __shfl_sync(0xffffffffu, wbase, 0);
-            if (wbase >= total) break;
-            const int my_item = wbase + grp * chunk + lane;
-            uint32_t entry = 0, beg = 0, end = 0;
-            double du = 0.0, thr = 0.0;
-            if (lane < chunk && my_item < total) {
-                entry = p.queue[par][my_item];
-                const int s = (int)(entry >> kVertexBits);
-                const uint32_t u = entry & kVertexMask;
-                du = __longlong_as_double((long long)ld_cg_u64(p.dist + (int64_t)s * n + u));
-                thr = __longlong_as_double((long long)ld_cg_u64((const unsigned long long*)&p.ctl[s].thr));
-                beg = (uint32_t)(__ldg(p.row_ptr + u) >> 1);
-                end = (uint32_t)(__ldg(p.row_ptr + u + 1) >> 1);
+        // ---- phase A: sweep the frontier bitmaps, relax the rows of the popped vertices ----
+        // A warp grabs 32 frontier words (1024 vertices of one slot) at a time, compacts their set bits and pops
+        // them 32 per chunk, so chunks stay full on sparse frontiers; the next grab is in flight meanwhile.
+        unsigned popped = 0;
+        const int64_t ngrab = (int64_t)B * ngroups;
+        u64* wcursor = &p.ctl[0].work[c_cur];
+        int64_t g = 0;
+        if (wlane == 0) g = (int64_t)atomicAdd(wcursor, 1ULL);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        while (g < ngrab) {
+            int64_t g_next = 0;
+            if (wlane == 0) g_next = (int64_t)atomicAdd(wcursor, 1ULL);
+            const int s = (int)(g / ngroups);
+            const int64_t w0 = (g - (int64_t)s * ngroups) * 32;
+            uint32_t word = 0;
+            if (!s_done[s]) word = ld_cg_u32(inq_cur + (int64_t)s * nwords + w0 + wlane);
+            if (!__ballot_sync(0xffffffffu, word != 0)) {
+                g = __shfl_sync(0xffffffffu, g_next, 0);
+                continue;
             }
-            // software pipeline: the pair loads of item j+1 are issued before item j's gathers are consumed
-            uint32_t nbeg = __shfl_sync(gmask, beg, 0, kGroup), nend = __shfl_sync(gmask, end, 0, kGroup);
-            uint4 n0 = pad4, n1 = pad4;
-            if (nbeg + lane < nend) n0 = ld_stream_v4(p.adj4 + nbeg + lane);
-            if (nbeg + lane + kGroup < nend) n1 = ld_stream_v4(p.adj4 + nbeg + lane + kGroup);
-            for (int j = 0; j < chunk; ++j) {
-                const uint32_t e_j = __shfl_sync(gmask, entry, j, kGroup);
-                const double du_j = __shfl_sync(gmask, du, j, kGroup);
-                const double thr_j = __shfl_sync(gmask, thr, j, kGroup);
-                const uint32_t beg_j = nbeg, end_j = nend;
-                uint4 e0 = n0, e1 = n1;
-                if (j + 1 < chunk) {
-                    nbeg = __shfl_sync(gmask, beg, j + 1, kGroup);
-                    nend = __shfl_sync(gmask, end, j + 1, kGroup);
-                    n0 = pad4;
-                    n1 = pad4;
-                    if (nbeg + lane < nend) n0 = ld_stream_v4(p.adj4 + nbeg + lane);
-                    if (nbeg + lane + kGroup < nend) n1 = ld_stream_v4(p.adj4 + nbeg + lane + kGroup);
-                }
-                const int64_t sbase = (int64_t)(e_j >> kVertexBits) * n;
-                unsigned long long* dist_s = p.dist + sbase;
-                int* state_s = p.state + sbase;
-                const uint32_t tag = e_j & ~kVertexMask;
-                for (uint32_t i = beg_j + lane;;) {
-                    // four independent distance gathers in flight, then the (rare) updates
-                    const unsigned long long d0 = ld_cg_u64(dist_s + e0.x), d1 = ld_cg_u64(dist_s + e0.z);
-                    const unsigned long long d2 = ld_cg_u64(dist_s + e1.x), d3 = ld_cg_u64(dist_s + e1.z);
-                    n_relax += (i < end_j ? 2 : 0) + (i + kGroup < end_j ? 2 : 0);
-                    relax_update(e0.x, du_j + (double)__uint_as_float(e0.y), d0, dist_s, state_s, thr_j, tag, active_mask,
-                                 wbuf, wcnt, qnext, qtail, n_improve);
-                    relax_update(e0.z, du_j + (double)__uint_as_float(e0.w), d1, dist_s, state_s, thr_j, tag, active_mask,
-                                 wbuf, wcnt, qnext, qtail, n_improve);
-                    relax_update(e1.x, du_j + (double)__uint_as_float(e1.y), d2, dist_s, state_s, thr_j, tag, active_mask,
-                                 wbuf, wcnt, qnext, qtail, n_improve);
-                    relax_update(e1.z, du_j + (double)__uint_as_float(e1.w), d3, dist_s, state_s, thr_j, tag, active_mask,
-                                 wbuf, wcnt, qnext, qtail, n_improve);
-                    i += 2 * kGroup;
-                    if (i >= end_j) break;  // rows longer than 4*kGroup pairs take further trips
-                    e0 = ld_stream_v4(p.adj4 + i);
-                    e1 = i + kGroup < end_j ? ld_stream_v4(p.adj4 + i + kGroup) : pad4;
-                }
-                stage_flush(wbuf, wcnt, qnext, qtail, kStage / 2);
+            u64* dist_s = p.dist + (int64_t)s * n;
+            u64* proc_s = p.proc + (int64_t)s * n;
+            uint32_t* ub_s = p.ub + (int64_t)s * n;
+            uint32_t* inqn_s = inq_next + (int64_t)s * nwords;
+            uint32_t* dirty_s = p.dirty + (int64_t)s * nwords;
+            if (word) {
+                inq_cur[(int64_t)s * nwords + w0 + wlane] = 0;  // consumed
+                red_and_u32(dirty_s + w0 + wlane, ~word);      // popped vertices are no longer "far"
             }
+            const double thr = s_thr[s];
+            bool near_any = false;
+            uint32_t wincl = __popc(word);
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, wincl, o);
+                if (wlane >= o) wincl += t;
+            }
+            const uint32_t wexcl = wincl - __popc(word);
+            const uint32_t nitems = __shfl_sync(0xffffffffu, wincl, 31);
+            for (uint32_t c0 = 0; c0 < nitems; c0 += 32) {
+                // ---- pop: lane = k-th set bit of the 32 words; relax its row only if its distance dropped since
+                //      it was last relaxed ----
+                const uint32_t k = c0 + wlane;
+                int wi = 0;  // word holding item k: first lane whose inclusive count exceeds k
+#pragma unroll
+                for (int st = 16; st; st >>= 1) {
+                    const uint32_t t = __shfl_sync(0xffffffffu, wincl, wi + st - 1);
+                    if (t <= k) wi += st;
+                }
+                wi = min(wi, 31);
+                const uint32_t wv = __shfl_sync(0xffffffffu, word, wi);
+                const uint32_t we = __shfl_sync(0xffffffffu, wexcl, wi);
+                uint32_t len = 0, beg = 0;
+                double du = 0.0;
+                if (k < nitems) {
+                    const int64_t u = (w0 + wi) * 32 + (int)__fns(wv, 0, (int)(k - we) + 1);
+                    const u64 cur = ld_cg_u64(dist_s + u);
+                    const u64 pr = ld_cg_u64(proc_s + u);
+                    const int64_t b64 = __ldg(p.row_ptr + u), e64 = __ldg(p.row_ptr + u + 1);
+                    if (cur < pr) {
+                        proc_s[u] = cur;
+                        len = (uint32_t)(e64 - b64);
+                        beg = (uint32_t)b64;
+                        du = __longlong_as_double((long long)cur);
+                        ++popped;
+                        // the row is streamed from HBM exactly once: start it towards L2 now, the trips below
+                        // then see L2 latency (rows longer than 4 lines are covered by the trip pipeline)
+                        const char* row = (const char*)(p.adj + b64);
+                        const int rb = (int)(len * 8u);
+#pragma unroll
+                        for (int o = 0; o < 512; o += 128)
+                            if (o < rb) prefetch_l2(row + o);
+                    }
+                }
+                uint32_t incl = len;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (wlane >= o) incl += t;
+                }
+                const uint32_t start = incl - len;
+                const uint32_t T = __shfl_sync(0xffffffffu, incl, 31);
+                const uint32_t rowoff = beg - start;  // adj index of flat position f inside this item = rowoff + f (mod 2^32)
+                if (T == 0) continue;
+                int jj[kPer];
+                uint2 e[kPer];
+                locate(0, start, len, own32, wlane, jj);
+#pragma unroll
+                for (int k = 0; k < kPer; ++k) {
+                    const uint32_t f = kPer * wlane + k;
+                    const uint32_t off = __shfl_sync(0xffffffffu, rowoff, jj[k]);
+                    e[k] = f < T ? ld_edge(p.adj + (uint32_t)(off + f), pol_stream) : pad_edge;
+                }
+                for (uint32_t tile = 0; tile < T; tile += kTile) {
+                    double duk[kPer];
+                    uint32_t ubv[kPer];
+#pragma unroll
+                    for (int k = 0; k < kPer; ++k) duk[k] = __shfl_sync(0xffffffffu, du, jj[k]);
+#pragma unroll
+                    for (int k = 0; k < kPer; ++k) ubv[k] = ld_ub(ub_s + e[k].x, pol_keep);
+                    n_relax += min((uint32_t)kPer, T - min(T, tile + kPer * wlane));
+                    // next trip's edge pairs are requested before this trip's gathers are consumed
+                    uint2 en[kPer];
+                    int jn[kPer];
+#pragma unroll
+                    for (int k = 0; k < kPer; ++k) en[k] = pad_edge, jn[k] = 0;
+                    if (tile + kTile < T) {
+                        locate(tile + kTile, start, len, own32, wlane, jn);
+#pragma unroll
+                        for (int k = 0; k < kPer; ++k) {
+                            const uint32_t f = tile + kTile + kPer * wlane + k;
+                            const uint32_t off = __shfl_sync(0xffffffffu, rowoff, jn[k]);
+                            if (f < T) en[k] = ld_edge(p.adj + (uint32_t)(off + f), pol_stream);
+                        }
+                    }
+#pragma unroll
+                    for (int k = 0; k < kPer; ++k) {
+                        const uint32_t v = e[k].x;
+                        const double cand = duk[k] + (double)__uint_as_float(e[k].y);
+                        // cand >= ub[v] (>= dist[v])  <=>  round_down_f32(cand) >= ub[v]: nothing to do
+                        if (__float_as_uint(__double2float_rd(cand)) < ubv[k]) {
+                            red_min_u64(dist_s + v, (u64)__double_as_longlong(cand));
+                            red_min_u32(ub_s + v, __float_as_uint(__double2float_ru(cand)), pol_keep);
+                            ++n_improve;
+                            if (cand < thr) {
+                                red_or_u32(inqn_s + (v >> 5), 1u << (v & 31));
+                                near_any = true;
+                            } else {
+                                red_or_u32(dirty_s + (v >> 5), 1u << (v & 31));
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int k = 0; k < kPer; ++k) e[k] = en[k], jj[k] = jn[k];
+                }
+            }
+            if (__any_sync(0xffffffffu, near_any) && wlane == 0) *(volatile int*)&p.ctl[s].active[c_next] = 1;
+            g = __shfl_sync(0xffffffffu, g_next, 0);
         }
-        stage_flush(wbuf, wcnt, qnext, qtail, 1);
-        for (int o = 16; o; o >>= 1) active_mask |= __shfl_xor_sync(0xffffffffu, active_mask, o);
-        if (wlane == 0)
-            for (unsigned m = active_mask; m; m &= m - 1) *(volatile int*)&p.ctl[__ffs(m) - 1].active[c_next] = 1;
         grid.sync();
         ++n_rounds;
+        if (p.stats && round < 120) {
+            popped = __reduce_add_sync(0xffffffffu, popped);
+            if (wlane == 0 && popped) atomicAdd(p.stats + 9 + 2 * round, (u64)popped);
+        }
         // ---- control: which slots ran dry? (uniform across the grid) ----
+        if (gtid < B) {  // scan accumulators of round-1 (index c_clear): every block read them before this sync
+            p.ctl[gtid].scan_min[c_clear] = F32_INF_BITS;
+            p.ctl[gtid].scan_pushed[c_clear] = 0;
+        }
         if (threadIdx.x == 0) s_flag = 0;
         __syncthreads();
         if (threadIdx.x < B) {
-            int s = threadIdx.x;
-            int need = (!ld_cg_s32(&p.ctl[s].done)) && ld_cg_s32(&p.ctl[s].active[c_next]) == 0;
+            const int s = threadIdx.x;
+            const int need = !s_done[s] && ld_cg_s32(&p.ctl[s].active[c_next]) == 0;
             s_need[s] = need;
             if (need) s_flag = 1;
         }
         __syncthreads();
-        const int any_scan = s_flag;
-        if (any_scan) {
+        if (s_flag) {
             ++n_scans;
-            // ---- phase B1: min dist over dirty vertices of each dry slot ----
+            // ---- phase B: raise the threshold of every dry slot and move its dirty vertices below it to the frontier ----
             for (int s = 0; s < B; ++s) {
                 if (!s_need[s]) continue;
-                const int64_t sbase = (int64_t)s * n;
-                unsigned long long m = D64_INF_BITS;
-                for (int64_t v = gtid; v < n; v += 4 * gthreads) {
-                    int st[4];
+                double thr_new = s_thr[s] + p.delta;
+                if (s_hint[s] > thr_new) thr_new = s_hint[s];
+                uint32_t* dirty_s = p.dirty + (int64_t)s * nwords;
+                uint32_t* inqn_s = inq_next + (int64_t)s * nwords;
+                const uint32_t* ub_s = p.ub + (int64_t)s * n;
+                uint32_t rem_min = F32_INF_BITS;
+                int pushed = 0;
+                for (int64_t w0 = gwarp * 32; w0 < nwords; w0 += nwarps * 32) {
+                    const uint32_t word = ld_cg_u32(dirty_s + w0 + wlane);
+                    uint32_t taken = 0;
+                    unsigned any = __ballot_sync(0xffffffffu, word != 0);
+                    while (any) {
+                        int src[4];
+                        uint32_t d[4];
+                        bool bit[4];
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) st[k] = v + k * gthreads < n ? ld_cg_s32(p.state + sbase + v + k * gthreads) : 0;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        if (st[k] == 1) {
-                            unsigned long long d = ld_cg_u64(p.dist + sbase + v + k * gthreads);
-                            m = d < m ? d : m;
+                        for (int k = 0; k < 4; ++k) {
+                            src[k] = any ? __ffs(any) - 1 : -1;
+                            any &= any - 1;
+                            const uint32_t wv = __shfl_sync(0xffffffffu, word, src[k] < 0 ? 0 : src[k]);
+                            bit[k] = src[k] >= 0 && ((wv >> wlane) & 1u);
+                            d[k] = F32_INF_BITS;
+                            if (bit[k]) d[k] = ld_ub(ub_s + (w0 + src[k]) * 32 + wlane, pol_keep);
                         }
-                }
-                for (int o = 16; o; o >>= 1) {
-                    unsigned long long t = __shfl_xor_sync(0xffffffffu, m, o);
-                    m = t < m ? t : m;
-                }
-                if (wlane == 0) s_red[threadIdx.x >> 5] = m;
-                __syncthreads();
-                if (threadIdx.x == 0) {
-                    for (int w = 1; w < kThreads / 32; ++w) m = s_red[w] < m ? s_red[w] : m;
-                    if (m != D64_INF_BITS) atomicMin(&p.ctl[s].far_min, m);
-                }
-                __syncthreads();
-            }
-            grid.sync();
-            // ---- phase B2: raise thr, queue dirty vertices below it (ballot-aggregated tail bump) ----
-            for (int s = 0; s < B; ++s) {
-                if (!s_need[s]) continue;
-                const unsigned long long fm = ld_cg_u64(&p.ctl[s].far_min);
-                if (fm == D64_INF_BITS) {  // nothing dirty: this source has converged
-                    if (gtid == 0) p.ctl[s].done = 1;
-                    continue;
-                }
-                const double thr_new = __longlong_as_double((long long)fm) + p.delta;
-                const int64_t sbase = (int64_t)s * n;
-                const int64_t n_round = (n + 31) & ~(int64_t)31;
-                for (int64_t v0 = gtid; v0 < n_round; v0 += 4 * gthreads) {
-                    int st[4];
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) st[k] = v0 + k * gthreads < n ? ld_cg_s32(p.state + sbase + v0 + k * gthreads) : 0;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const int64_t v = v0 + k * gthreads;
-                        if (v - wlane >= n_round) break;  // warp-uniform
-                        bool take = false;
-                        if (st[k] == 1) {
-                            double d = __longlong_as_double((long long)ld_cg_u64(p.dist + sbase + v));
-                            take = d < thr_new;
-                        }
-                        const unsigned bal = __ballot_sync(0xffffffffu, take);
-                        if (bal) {
-                            int wbase = 0;
-                            if (wlane == 0) wbase = atomicAdd(qtail, __popc(bal));
-                            wbase = __shfl_sync(0xffffffffu, wbase, 0);
-                            if (take) {
-                                p.state[sbase + v] = 2;
-                                qnext[wbase + __popc(bal & ((1u << wlane) - 1))] = ((uint32_t)s << kVertexBits) | (uint32_t)v;
-                            }
+                        for (int k = 0; k < 4; ++k) {
+                            const bool take = bit[k] && (double)__uint_as_float(d[k]) < thr_new;
+                            const unsigned bal = __ballot_sync(0xffffffffu, take);
+                            if (wlane == src[k]) taken |= bal;
+                            pushed += __popc(bal);
+                            if (bit[k] && !take) rem_min = min(rem_min, d[k]);
                         }
                     }
+                    if (taken) {
+                        dirty_s[w0 + wlane] = word & ~taken;
+                        red_or_u32(inqn_s + w0 + wlane, taken);
+                    }
                 }
-                if (gtid == 0) {
-                    p.ctl[s].thr = thr_new;
-                    p.ctl[s].active[c_next] = 1;
+                rem_min = __reduce_min_sync(0xffffffffu, rem_min);
+                if (wlane == 0) {
+                    if (rem_min != F32_INF_BITS) atomicMin(&p.ctl[s].scan_min[c_cur], rem_min);
+                    // (active[c_next] must not be touched here: slower blocks may still be reading it to decide
+                    //  whether to enter this phase, and its grid.sync, at all)
+                    if (pushed) atomicAdd(&p.ctl[s].scan_pushed[c_cur], pushed);
                 }
+                if (gtid == 0) p.ctl[s].thr2[(s_epoch[s] + 1) & 1] = thr_new;
             }
             grid.sync();
+            if (threadIdx.x < B && s_need[threadIdx.x]) {  // identical in every block
+                const int s = threadIdx.x;
+                const int pushed = ld_cg_s32(&p.ctl[s].scan_pushed[c_cur]);
+                const uint32_t mn = ld_cg_u32(&p.ctl[s].scan_min[c_cur]);
+                s_epoch[s] += 1;
+                s_hint[s] = 0.0;
+                if (pushed == 0) {
+                    if (mn == F32_INF_BITS) s_done[s] = 1;  // frontier empty and nothing dirty: converged
+                    else s_hint[s] = (double)__uint_as_float(mn) + p.delta;  // jump over the gap
+                }
+            }
+            __syncthreads();
         }
-        // ---- termination test (uniform: `done` only changes in B2, which ends with a grid.sync) ----
+        // ---- termination test (uniform) ----
         if (threadIdx.x == 0) s_alldone = 1;
         __syncthreads();
-        if (threadIdx.x < B && !ld_cg_s32(&p.ctl[threadIdx.x].done)) s_alldone = 0;
+        if (threadIdx.x < B && !s_done[threadIdx.x]) s_alldone = 0;
         __syncthreads();
         if (s_alldone) break;
+        if (round >= p.max_rounds) {  // uniform
+            if (gtid == 0) *p.failed = 1;
+            break;
+        }
     }
 
     // ---- finalize ----
@@ -384,21 +500,22 @@ __global__ void __launch_bounds__(kThreads, GEOCB_MINBLOCKS) sssp_kernel(SsspPar
         for (int64_t i = gtid; i < (int64_t)B * n; i += gthreads)
             p.out_d32[i] = __double2float_rn(__longlong_as_double((long long)p.dist[i]));
         if (p.out_pred) {
-            const int64_t ggroup = gtid / kGroup, ngroups = gthreads / kGroup;
-            for (int64_t item = ggroup; item < (int64_t)B * n; item += ngroups) {
+            constexpr int kGroup = 8;  // lanes per vertex; shuffles name only the group's own lanes
+            const int lane = threadIdx.x & (kGroup - 1);
+            const unsigned gmask = ((1u << kGroup) - 1u) << (((threadIdx.x & 31) / kGroup) * kGroup);
+            const int64_t ggroup = gtid / kGroup, ngroupsp = gthreads / kGroup;
+            for (int64_t item = ggroup; item < (int64_t)B * n; item += ngroupsp) {
                 const int s = (int)(item / n);
                 const int64_t v = item - (int64_t)s * n;
-                const unsigned long long* dist_s = p.dist + (int64_t)s * n;
-                const unsigned long long dv = dist_s[v];
+                const u64* dist_s = p.dist + (int64_t)s * n;
+                const u64 dv = dist_s[v];
                 int best = 0x7fffffff;
                 if (dv != D64_INF_BITS && v != p.sources[s]) {
-                    const int64_t beg = p.row_ptr[v] >> 1, end = p.row_ptr[v + 1] >> 1;
+                    const int64_t beg = p.row_ptr[v], end = p.row_ptr[v + 1];
                     for (int64_t i = beg + lane; i < end; i += kGroup) {
-                        uint4 e = ld_stream_v4(p.adj4 + i);
-                        double c0 = __longlong_as_double((long long)dist_s[e.x]) + (double)__uint_as_float(e.y);
-                        double c1 = __longlong_as_double((long long)dist_s[e.z]) + (double)__uint_as_float(e.w);
-                        if ((unsigned long long)__double_as_longlong(c0) == dv && (int)e.x < best) best = (int)e.x;
-                        if ((unsigned long long)__double_as_longlong(c1) == dv && (int)e.z < best) best = (int)e.z;
+                        const uint2 e = p.adj[i];
+                        const double c0 = __longlong_as_double((long long)dist_s[e.x]) + (double)__uint_as_float(e.y);
+                        if ((u64)__double_as_longlong(c0) == dv && (int)e.x < best) best = (int)e.x;
                     }
                 }
                 for (int o = kGroup / 2; o; o >>= 1) best = min(best, __shfl_xor_sync(gmask, best, o, kGroup));
@@ -407,17 +524,21 @@ __global__ void __launch_bounds__(kThreads, GEOCB_MINBLOCKS) sssp_kernel(SsspPar
         }
     }
     if (p.stats) {
-        for (int o = 16; o; o >>= 1) {
-            n_relax += __shfl_xor_sync(0xffffffffu, n_relax, o);
-            n_improve += __shfl_xor_sync(0xffffffffu, n_improve, o);
+        if (gtid == 0) {
+            u64 t;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+            p.stats[6] = t;
+            p.stats[7] = (u64)n_rounds;
         }
-        if ((threadIdx.x & 31) == 0) {
-            atomicAdd(p.stats + 0, (unsigned long long)n_relax);
-            atomicAdd(p.stats + 3, (unsigned long long)n_improve);
+        n_relax = __reduce_add_sync(0xffffffffu, n_relax);
+        n_improve = __reduce_add_sync(0xffffffffu, n_improve);
+        if (wlane == 0) {
+            atomicAdd(p.stats + 0, (u64)n_relax);
+            atomicAdd(p.stats + 3, (u64)n_improve);
         }
         if (gtid == 0) {
-            atomicAdd(p.stats + 1, (unsigned long long)n_rounds);
-            atomicAdd(p.stats + 2, (unsigned long long)n_scans);
+            atomicAdd(p.stats + 1, (u64)n_rounds);
+            atomicAdd(p.stats + 2, (u64)n_scans);
         }
     }
 }
@@ -437,27 +558,64 @@ int coop_grid(int* grid_out) {
 }
 
 struct WsLayout {
-    int64_t dist, state, q0, q1, ctl, gctl, stats, total;
+    int64_t dist, proc, ub, inq0, inq1, dirty, ctl, stats, total, nwords;
 };
 WsLayout ws_layout(int64_t n, int slots, bool own_dist) {
     WsLayout w;
     int64_t off = 0;
+    w.nwords = align_up((n + 31) / 32, 32);
     w.dist = off;
     if (own_dist) off += align_up((int64_t)slots * n * 8, 256);
-    w.state = off;
+    w.proc = off;
+    off += align_up((int64_t)slots * n * 8, 256);
+    w.ub = off;
     off += align_up((int64_t)slots * n * 4, 256);
-    w.q0 = off;
-    off += align_up((int64_t)slots * n * 4, 256);
-    w.q1 = off;
-    off += align_up((int64_t)slots * n * 4, 256);
+    w.inq0 = off;
+    off += align_up((int64_t)slots * w.nwords * 4, 256);
+    w.inq1 = off;
+    off += align_up((int64_t)slots * w.nwords * 4, 256);
+    w.dirty = off;
+    off += align_up((int64_t)slots * w.nwords * 4, 256);
     w.ctl = off;
     off += align_up((int64_t)kMaxSlots * sizeof(SlotCtl), 256);
-    w.gctl = off;
-    off += 256;
     w.stats = off;
-    off += 256;
+    off += 2048;  // 4 counters + a (time, popped vertices) trace of the last launch's first 120 rounds
     w.total = off;
     return w;
+}
+
+void fill_params(SsspParams& p, const WsLayout& w, char* ws, const int64_t* row_ptr, const void* adj, int64_t n,
+                 double delta) {
+    memset(&p, 0, sizeof(p));
+    p.row_ptr = row_ptr;
+    p.adj = (const uint2*)adj;
+    p.n = n;
+    p.nwords = w.nwords;
+    p.delta = delta;
+    p.dist = (u64*)(ws + w.dist);
+    p.proc = (u64*)(ws + w.proc);
+    p.ub = (uint32_t*)(ws + w.ub);
+    p.inq[0] = (uint32_t*)(ws + w.inq0);
+    p.inq[1] = (uint32_t*)(ws + w.inq1);
+    p.dirty = (uint32_t*)(ws + w.dirty);
+    p.ctl = (SlotCtl*)(ws + w.ctl);
+    p.failed = (int*)(ws + w.stats + 40);
+    const char* env = getenv("GEOCB_SSSP_MAX_ROUNDS");
+    const int64_t lim = env ? atoll(env) : 8 * n + 4096;
+    p.max_rounds = (int)(lim < 0x7fffff00 ? lim : 0x7fffff00);
+}
+
+__global__ void voronoi_init_kernel(int64_t n, int64_t nwords, u64* d64, float* d32, int32_t* label, u64* proc,
+                                    uint32_t* ub, uint32_t* inq0, uint32_t* inq1, uint32_t* dirty) {
+    const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nt = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = t0; i < n; i += nt) {
+        d64[i] = D64_INF_BITS;
+        d32[i] = __uint_as_float(F32_INF_BITS);
+        label[i] = -1;
+        proc[i] = D64_INF_BITS;
+        ub[i] = F32_INF_BITS;
+    }
+    for (int64_t i = t0; i < nwords; i += nt) inq0[i] = inq1[i] = dirty[i] = 0;
 }
 
 }  // namespace
@@ -476,7 +634,7 @@ GEOCB_API int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t 
                                double delta, int slots, void* workspace, int64_t workspace_bytes, float* out_d32,
                                int32_t* out_pred, int64_t* stats_host, void* stream) {
     ARG_CHECK(row_ptr && adj && sources && out_d32 && workspace);
-    ARG_CHECK(n > 0 && n < (1LL << kVertexBits) && S > 0 && slots >= 1 && slots <= kMaxSlots && delta > 0);
+    ARG_CHECK(n > 0 && n < (1LL << 31) - 64 && S > 0 && slots >= 1 && slots <= kMaxSlots && delta > 0);
     WsLayout w = ws_layout(n, slots, true);
     if (workspace_bytes < w.total) {
         geocb_set_error("sssp workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)w.total);
@@ -487,47 +645,44 @@ GEOCB_API int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t 
     int grid = 0;
     int rc = coop_grid(&grid);
     if (rc) return rc;
-    CU_TRY(cudaMemsetAsync(ws + w.stats, 0, 32, st));
+    CU_TRY(cudaMemsetAsync(ws + w.stats, 0, 2048, st));
     for (int s0 = 0; s0 < S; s0 += slots) {
         SsspParams p;
-        memset(&p, 0, sizeof(p));
-        p.row_ptr = row_ptr;
-        p.adj4 = (const uint4*)adj;
-        p.n = n;
+        fill_params(p, w, ws, row_ptr, adj, n, delta);
         p.nslots = (S - s0) < slots ? (S - s0) : slots;
-        p.delta = delta;
-        p.dist = (unsigned long long*)(ws + w.dist);
-        p.state = (int*)(ws + w.state);
-        p.queue[0] = (uint32_t*)(ws + w.q0);
-        p.queue[1] = (uint32_t*)(ws + w.q1);
-        p.ctl = (SlotCtl*)(ws + w.ctl);
-        p.gctl = (GlobalCtl*)(ws + w.gctl);
-        p.stats = (unsigned long long*)(ws + w.stats);
+        p.stats = (u64*)(ws + w.stats);
         p.sources = sources + s0;
         p.out_d32 = out_d32 + (int64_t)s0 * n;
         p.out_pred = out_pred ? out_pred + (int64_t)s0 * n : nullptr;
         p.voronoi = 0;
+        if (s0 + slots < S || s0 > 0) CU_TRY(cudaMemsetAsync(ws + w.stats + 64, 0, 2048 - 64, st));  // trace = last launch
         void* args[] = {&p};
         CU_TRY(cudaLaunchCooperativeKernel((void*)sssp_kernel, dim3(grid), dim3(kThreads), args, 0, st));
     }
     if (stats_host) CU_TRY(cudaMemcpyAsync(stats_host, ws + w.stats, 32, cudaMemcpyDeviceToHost, st));
+    int failed = 0;
+    CU_TRY(cudaMemcpyAsync(&failed, ws + w.stats + 40, 4, cudaMemcpyDeviceToHost, st));
     CU_TRY(cudaStreamSynchronize(st));
+    if (failed) {
+        geocb_set_error("sssp_kernel did not converge within the round limit");
+        return GEOCB_ERR_OVERFLOW;
+    }
     return 0;
 }
 
-namespace {
-__global__ void voronoi_init_kernel(int64_t n, unsigned long long* d64, float* d32, int32_t* label) {
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        d64[i] = D64_INF_BITS;
-        d32[i] = __uint_as_float(F32_INF_BITS);
-        label[i] = -1;
+GEOCB_API int geocb_voronoi_init(int64_t n, double* dmin64, float* dmin32, int32_t* label, void* workspace,
+                                 int64_t workspace_bytes, void* stream) {
+    ARG_CHECK(n > 0 && dmin64 && dmin32 && label && workspace);
+    WsLayout w = ws_layout(n, 1, false);
+    if (workspace_bytes < w.total) {
+        geocb_set_error("voronoi workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)w.total);
+        return GEOCB_ERR_WORKSPACE;
     }
-}
-}  // namespace
-
-GEOCB_API int geocb_voronoi_init(int64_t n, double* dmin64, float* dmin32, int32_t* label, void* stream) {
-    ARG_CHECK(n > 0 && dmin64 && dmin32 && label);
-    voronoi_init_kernel<<<592, 256, 0, (cudaStream_t)stream>>>(n, (unsigned long long*)dmin64, dmin32, label);
+    char* ws = (char*)workspace;
+    CU_TRY(cudaMemsetAsync(ws + w.stats, 0, 2048, (cudaStream_t)stream));
+    voronoi_init_kernel<<<592, 256, 0, (cudaStream_t)stream>>>(
+        n, w.nwords, (u64*)dmin64, dmin32, label, (u64*)(ws + w.proc), (uint32_t*)(ws + w.ub), (uint32_t*)(ws + w.inq0),
+        (uint32_t*)(ws + w.inq1), (uint32_t*)(ws + w.dirty));
     KERNEL_CHECK();
     return 0;
 }
@@ -536,7 +691,7 @@ GEOCB_API int geocb_voronoi_insert(const int64_t* row_ptr, const void* adj, int6
                                    double delta, double* dmin64, float* dmin32, int32_t* label, void* workspace,
                                    int64_t workspace_bytes, void* stream) {
     ARG_CHECK(row_ptr && adj && dmin64 && dmin32 && label && workspace);
-    ARG_CHECK(n > 0 && n < (1LL << kVertexBits) && center >= 0 && center < n && delta > 0);
+    ARG_CHECK(n > 0 && n < (1LL << 31) - 64 && center >= 0 && center < n && delta > 0);
     WsLayout w = ws_layout(n, 1, false);
     if (workspace_bytes < w.total) {
         geocb_set_error("voronoi workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)w.total);
@@ -546,19 +701,12 @@ GEOCB_API int geocb_voronoi_insert(const int64_t* row_ptr, const void* adj, int6
     int grid = 0;
     int rc = coop_grid(&grid);
     if (rc) return rc;
+    // workspace contract: initialised by geocb_voronoi_init and passed unchanged to every insert (proc, ub persist;
+    // the frontier and dirty bitmaps are all-zero again when the kernel exits)
     SsspParams p;
-    memset(&p, 0, sizeof(p));
-    p.row_ptr = row_ptr;
-    p.adj4 = (const uint4*)adj;
-    p.n = n;
+    fill_params(p, w, ws, row_ptr, adj, n, delta);
     p.nslots = 1;
-    p.delta = delta;
-    p.dist = (unsigned long long*)dmin64;
-    p.state = (int*)(ws + w.state);  // must be all-zero on entry; the kernel leaves it all-zero
-    p.queue[0] = (uint32_t*)(ws + w.q0);
-    p.queue[1] = (uint32_t*)(ws + w.q1);
-    p.ctl = (SlotCtl*)(ws + w.ctl);
-    p.gctl = (GlobalCtl*)(ws + w.gctl);
+    p.dist = (u64*)dmin64;
     p.stats = nullptr;
     p.voronoi = 1;
     p.center = center;
