@@ -206,19 +206,31 @@ __device__ __forceinline__ double block_scan_f64(double v, double* total) {
     return base + inc;  // inclusive
 }
 // q[i] = float64( p[i] / total )  (float32 divide, kmeans_optimized.py:60) ; per-tile fp64 sums
-__global__ void cdf_tile_sums_kernel(const float* p, const float* total, int64_t n, double* tile_sums) {
+// `fine` counts the elements that can make the sequential fp64 cumsum round at all: q is a float32, i.e. a
+// multiple of 2^-23*2^floor(log2 q); while every partial sum stays below 2 its ulp is at most 2^-52, so adding
+// q >= 2^-28 to a multiple of 2^-52 is exact.  Only q < 2^-28 (and the <= 64 binade crossings of the running
+// sum) can round, each by at most 2^-53: that gives the rigorous tolerance cdf_locate_kernel uses.
+__global__ void cdf_tile_sums_kernel(const float* p, const float* total, int64_t n, double* tile_sums,
+                                     unsigned long long* fine) {
     const float tot = *total;
     const int64_t base = (int64_t)blockIdx.x * kCdfTile + (int64_t)threadIdx.x * kCdfItems;
     double s = 0.0;
+    unsigned nf = 0;
     for (int i = 0; i < kCdfItems; ++i)
-        if (base + i < n) s += (double)__fdiv_rn(p[base + i], tot);
+        if (base + i < n) {
+            const double q = (double)__fdiv_rn(p[base + i], tot);
+            s += q;
+            nf += (q > 0.0 && q < 3.7252902984619141e-09) ? 1u : 0u;  // 2^-28
+        }
+    nf = __reduce_add_sync(0xffffffffu, nf);
+    if ((threadIdx.x & 31) == 0 && nf) atomicAdd(fine, (unsigned long long)nf);
     double t;
     block_scan_f64(s, &t);
     if (threadIdx.x == 0) tile_sums[blockIdx.x] = t;
 }
 // result: [0] index, [1] ambiguous flag
 __global__ void cdf_locate_kernel(const float* p, const float* total, int64_t n, double u, double* tile_sums,
-                                  int64_t ntiles, long long* result) {
+                                  int64_t ntiles, long long* result, const unsigned long long* fine) {
     __shared__ double s_excl, s_last;
     __shared__ long long s_tile;
     const float tot = *total;
@@ -253,7 +265,11 @@ __global__ void cdf_locate_kernel(const float* p, const float* total, int64_t n,
     }
     __syncthreads();
     const double last = s_last, target = u * last, excl = s_excl;
-    const double tol = 3.0 * (double)n * 1.1102230246251565e-16 * last;
+    // |sequential - exact| <= (fine + 64) * 2^-53 and |this scan - exact| <= (ntiles + 64) * 2^-53 while last < 2
+    // (every addition of non-negative terms rounds by at most half an ulp of a sum below 2); the comparison
+    // fl(c_i / c_last) > u differs from c_i > u * c_last by a few more ulps.  Doubled for slack.
+    double tol = 3.0 * (double)n * 1.1102230246251565e-16 * last;  // worst-case bound, used if last >= 2
+    if (last < 2.0) tol = 4.0 * ((double)*fine + (double)ntiles + 144.0) * 1.1102230246251565e-16;
     const int64_t base = s_tile * kCdfTile + (int64_t)threadIdx.x * kCdfItems;
     double q[kCdfItems], s = 0.0;
     for (int i = 0; i < kCdfItems; ++i) {
@@ -404,8 +420,9 @@ GEOCB_API int geocb_kpp_draw(const float* dmin32, const uint8_t* is_center, int6
     int rc = run_pairwise(src, plan, n_leaves_upper, vals, total, st);
     if (rc) return rc;
     const int64_t ntiles = (n + kCdfTile - 1) / kCdfTile;
-    cdf_tile_sums_kernel<<<(unsigned)ntiles, kCdfThreads, 0, st>>>(p, total, n, tile_sums);
-    cdf_locate_kernel<<<1, kCdfThreads, 0, st>>>(p, total, n, u, tile_sums, ntiles, result);
+    unsigned long long* fine = (unsigned long long*)(ws + w.scalars + 48);
+    cdf_tile_sums_kernel<<<(unsigned)ntiles, kCdfThreads, 0, st>>>(p, total, n, tile_sums, fine);
+    cdf_locate_kernel<<<1, kCdfThreads, 0, st>>>(p, total, n, u, tile_sums, ntiles, result, fine);
     KERNEL_CHECK();
     long long host[2];
     float tot_host;
