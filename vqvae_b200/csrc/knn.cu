@@ -16,7 +16,9 @@
 //         >= T, hence exact score >= T - eps; if the kq-th exact score is not < T - eps the row is
 //         redone by pass 3.
 // pass 3  exact fp64 brute force for uncertified rows (one CTA per row; rare).
+#include <stdlib.h>
 #include "common.cuh"
+#include "knn_tc.cuh"
 
 namespace {
 
@@ -217,7 +219,8 @@ __device__ __forceinline__ bool key_less(double d0, int i0, double d1, int i1) {
 template <int L>
 __global__ void knn_rerank_kernel(const float* __restrict__ z, int64_t M, int d, int64_t q_lo, int64_t nq, int kq,
                                   const int32_t* cand_idx, const float* cand_thr, const unsigned int* max_nrm_bits,
-                                  int32_t* out_idx, float* out_dist, int32_t* unsafe_rows, int32_t* n_unsafe) {
+                                  double eps_unit, int32_t* out_idx, float* out_dist, int32_t* unsafe_rows,
+                                  int32_t* n_unsafe) {
     constexpr int PER = L / 32;
     const int64_t q = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
@@ -229,6 +232,7 @@ __global__ void knn_rerank_kernel(const float* __restrict__ z, int64_t M, int d,
 #pragma unroll
     for (int e = 0; e < PER; ++e) {
         id[e] = cand_idx[q * L + e * 32 + lane];
+        if (id[e] >= M) id[e] = -1;  // pad rows of the tensor-core filter
         d2[e] = id[e] >= 0 ? exact_d2(a, z + (int64_t)id[e] * d, d) : __longlong_as_double(D64_INF_BITS);
         if (id[e] < 0) id[e] = 0x7fffffff;
         nvalid += __popc(__ballot_sync(0xffffffffu, id[e] != 0x7fffffff));
@@ -273,7 +277,9 @@ __global__ void knn_rerank_kernel(const float* __restrict__ z, int64_t M, int d,
             double a2 = 0.0;
             for (int i = 0; i < d; ++i) a2 = fma((double)a[i], (double)a[i], a2);
             const double b2 = (double)__uint_as_float(*max_nrm_bits) * (1.0 + 1e-6);
-            const double eps = (2.0 * d + 8.0) * 5.9604644775390625e-08 * (b2 + 2.0 * sqrt(a2 * b2)) * 1.01;
+            // filter score error bound: eps_unit = (2d+8)*2^-24*1.01 for the fp32 FFMA2 filter, 2^-17 for the
+            // 3xTF32 tensor-core filter (dropped lo*lo term, tf32 truncation of lo, fp32 accumulation of 56 terms)
+            const double eps = eps_unit * (b2 + 2.0 * sqrt(a2 * b2));
             const double T = (double)cand_thr[q];
             safe = (__longlong_as_double((long long)kall) - a2) < (T - eps);
         }
@@ -395,7 +401,30 @@ GEOCB_API int geocb_knn_topk(const float* z, int64_t M, int d, int64_t q_lo, int
     while (dpad < d) dpad <<= 1;
     const int L = kq <= 26 ? 32 : 64;
     const bool fast = dpad <= 64 && kq <= 56;
-    if (fast) {
+    const double eps_ffma = (2.0 * d + 8.0) * 5.9604644775390625e-08 * 1.01;
+    const char* tc_env = getenv("GEOCB_KNN_TC");
+    const bool use_tc = d <= 16 && kq <= 26 && !(tc_env && tc_env[0] == '0');
+    if (use_tc) {
+        // tcgen05 filter (knn_tc.cu) -> same exact re-rank / certificate / fallback as the FFMA2 path
+        const int64_t Mp = knn_tc_padded_candidates(M), nqp = knn_tc_padded_queries(nq);
+        float *bimg, *aimg, *cand_thr;
+        int32_t *cand_idx, *unsafe_rows;
+        if ((rc = sx.alloc((void**)&bimg, (size_t)knn_tc_image_floats(Mp) * 4)) ||
+            (rc = sx.alloc((void**)&aimg, (size_t)knn_tc_image_floats(nqp) * 4)) ||
+            (rc = sx.alloc((void**)&cand_idx, (size_t)nq * 32 * 4)) || (rc = sx.alloc((void**)&cand_thr, (size_t)nq * 4)) ||
+            (rc = sx.alloc((void**)&unsafe_rows, (size_t)nq * 4)))
+            return rc;
+        unsigned int* max_nrm = (unsigned int*)(unsafe_cnt + 1);
+        if ((rc = knn_filter_tc(z, M, d, q_lo, nq, bimg, aimg, max_nrm, cand_idx, cand_thr, st))) return rc;
+        const unsigned rb = (unsigned)((nq * 32 + 255) / 256);
+        knn_rerank_kernel<32><<<rb, 256, 0, st>>>(z, M, d, q_lo, nq, kq, cand_idx, cand_thr, max_nrm,
+                                                   7.62939453125e-06 /* 2^-17 */, out_idx, out_dist, unsafe_rows,
+                                                   unsafe_cnt);
+        KERNEL_CHECK();
+        knn_exact_kernel<<<di.sm_count * 4, 256, 0, st>>>(z, M, d, q_lo, kq, unsafe_rows, unsafe_cnt, 0, out_idx,
+                                                           out_dist);
+        KERNEL_CHECK();
+    } else if (fast) {
         const int tile_c = kTileBytes / (dpad * 4);
         const int64_t Mp = align_up(M, tile_c);
         float *zt, *nrm, *cand_thr;
@@ -412,11 +441,11 @@ GEOCB_API int geocb_knn_topk(const float* z, int64_t M, int d, int64_t q_lo, int
         if (rc) return rc;
         const unsigned rb = (unsigned)((nq * 32 + 255) / 256);
         if (L == 32)
-            knn_rerank_kernel<32><<<rb, 256, 0, st>>>(z, M, d, q_lo, nq, kq, cand_idx, cand_thr, max_nrm, out_idx,
-                                                       out_dist, unsafe_rows, unsafe_cnt);
+            knn_rerank_kernel<32><<<rb, 256, 0, st>>>(z, M, d, q_lo, nq, kq, cand_idx, cand_thr, max_nrm, eps_ffma,
+                                                       out_idx, out_dist, unsafe_rows, unsafe_cnt);
         else
-            knn_rerank_kernel<64><<<rb, 256, 0, st>>>(z, M, d, q_lo, nq, kq, cand_idx, cand_thr, max_nrm, out_idx,
-                                                       out_dist, unsafe_rows, unsafe_cnt);
+            knn_rerank_kernel<64><<<rb, 256, 0, st>>>(z, M, d, q_lo, nq, kq, cand_idx, cand_thr, max_nrm, eps_ffma,
+                                                       out_idx, out_dist, unsafe_rows, unsafe_cnt);
         KERNEL_CHECK();
         knn_exact_kernel<<<di.sm_count * 4, 256, 0, st>>>(z, M, d, q_lo, kq, unsafe_rows, unsafe_cnt, 0, out_idx,
                                                            out_dist);

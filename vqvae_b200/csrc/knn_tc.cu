@@ -1,0 +1,315 @@
+// knn_tc.cu -- kNN filter pass on the 5th-generation tensor cores (tcgen05 + TMEM), d <= 16.
+//
+// Replaces pass 1 of knn.cu (the fp32 FFMA2 filter) for the reference's kNN query
+// (src/geo/knn_graph_optimized.py:39-42).  Only the contraction runs on tensor cores:
+//     score(q,c) = |c|^2 - 2 q.c      (|q|^2 is constant per row and dropped)
+// is one tf32 GEMM with fp32-grade accuracy by splitting every operand into tf32 hi + lo parts
+// (hi*hi + lo*hi + hi*lo, the lo*lo term is below 2^-22) and folding |c|^2 in as one more K-step:
+//     A row (query)     = [ -2a_hi (16) | -2a_lo (16) | 1 1 0 0 0 0 0 0 ]      40 floats
+//     B row (candidate) = [   b_hi (16) |   b_lo (16) | n_hi n_lo 0 0 0 0 0 0 ]
+//     7 MMAs of K=8 per tile:  hi.hi (2)  lo.hi (2)  hi.lo (2)  ones.norm (1)
+// Operand tiles are stored in global memory already in the UMMA canonical K-major no-swizzle image
+// (8x16-byte core matrices; LBO = 128 rows * 16 B between K-groups, SBO = 128 B between 8-row groups),
+// so one 1-D TMA bulk copy (cp.async.bulk + mbarrier) stages a 128-candidate tile (20 KB).
+// One CTA owns 256 query rows = two 128-row A tiles, so each staged B tile feeds two accumulators
+// (halves the L2->SM operand traffic); accumulators are double-buffered in TMEM (4 x 128 columns = all 512).
+//   warp 8  lane 0 : TMA producer (A tiles once, then the B tile ring)
+//   warp 9  lane 0 : tcgen05.mma issuer; tcgen05.commit releases smem stages / publishes accumulators
+//   warps 0-7      : epilogue -- thread = query row: tcgen05.ld 32 scores at a time, a min-tree screens them
+//                    against the row's current threshold, the rare survivors enter the row's L-entry list.
+// Output is the same (cand_idx, cand_thr) pair knn.cu's exact fp64 re-rank + certificate consume.
+#include "common.cuh"
+#include "knn_tc.cuh"
+
+namespace {
+
+constexpr int kRowFloats = 40;              // floats per operand row image
+constexpr int kKGroups = kRowFloats / 4;    // 16-byte K-groups per row
+constexpr int kTileRows = 128;
+constexpr int kLBO = kTileRows * 16;        // bytes between K-groups
+constexpr int kTileBytes = kKGroups * kLBO; // 20480
+constexpr int kStages = 4;
+constexpr int kL = 32;                      // list length (kq <= 26)
+constexpr int kRowsPerCta = 256;
+constexpr int kThreads = 320;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// bounded wait: a protocol bug must trap (error returned to the caller), never hang the device
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok = 0;
+    for (uint32_t spin = 0; !ok; ++spin) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+        if (spin > (1u << 26)) __trap();
+    }
+}
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ float to_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+// UMMA shared-memory descriptor, K-major, no swizzle (cute::UMMA::SmemDescriptor): start>>4 [0,14),
+// LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), layout_type=0 [61,64)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | ((uint64_t)(kLBO >> 4) << 16) | ((uint64_t)(128 >> 4) << 32) |
+           (1ULL << 46);
+}
+// instruction descriptor (cute::UMMA::InstrDescriptor): D=f32, A=B=tf32, K-major both, M=128, N=128
+constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// byte offset of element (row r, float k) inside a 128-row operand tile image
+__device__ __forceinline__ int img_off(int r, int k) { return (k >> 2) * kLBO + (r >> 3) * 128 + (r & 7) * 16 + (k & 3) * 4; }
+
+// ------------------------------------------------------------------ prep ----
+// one thread per (row, K-group): writes the candidate image (all M rows, padded to whole tiles) and, for rows
+// inside [q_lo, q_lo+nq_pad), the query image.  Pad candidates get a huge finite norm so they are never kept.
+__global__ void knn_tc_prep_kernel(const float* __restrict__ z, int64_t M, int d, int64_t Mp, int64_t q_lo, int64_t nq,
+                                   int64_t nq_pad, float* bimg, float* aimg, unsigned int* max_nrm_bits) {
+    const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t row = gid / kKGroups;
+    const int kg = (int)(gid % kKGroups);
+    const bool is_b = row < Mp;
+    const int64_t qrow = row - Mp;  // rows >= Mp enumerate the query image
+    if (!is_b && qrow >= nq_pad) return;
+    const int64_t src = is_b ? row : q_lo + qrow;
+    const bool live = is_b ? row < M : qrow < nq;
+    float out[4] = {0.f, 0.f, 0.f, 0.f};
+    if (kg < 8) {  // hi (kg 0-3) / lo (kg 4-7) parts of 4 coordinates
+        const int c0 = (kg & 3) * 4;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float v = (live && c0 + i < d) ? z[src * d + c0 + i] : 0.f;
+            if (!is_b) v *= -2.0f;
+            const float hi = to_tf32(v);
+            out[i] = kg < 4 ? hi : v - hi;
+        }
+    } else if (kg == 8) {
+        if (is_b) {
+            float s = 0.f;
+            if (live) {
+                for (int i = 0; i < d; ++i) s = __fmaf_rn(z[src * d + i], z[src * d + i], s);
+                atomicMax(max_nrm_bits, __float_as_uint(s));
+            } else {
+                s = 3.0e38f;
+            }
+            const float hi = to_tf32(s);
+            out[0] = hi;
+            out[1] = live ? s - hi : 0.f;
+        } else {
+            out[0] = 1.f;
+            out[1] = 1.f;
+        }
+    }
+    const int64_t tile = (is_b ? row : qrow) / kTileRows;
+    const int r = (int)((is_b ? row : qrow) % kTileRows);
+    float* base = (is_b ? bimg : aimg) + tile * (kTileBytes / 4);
+    *(float4*)((char*)base + img_off(r, kg * 4)) = make_float4(out[0], out[1], out[2], out[3]);
+}
+
+// ------------------------------------------------------------------ filter ----
+struct alignas(8) TcBars {
+    uint64_t a_full, full[kStages], empty[kStages], tmem_full[2], tmem_empty[2];
+    uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float* __restrict__ aimg,
+                                                                     const float* __restrict__ bimg, int64_t Mp,
+                                                                     int64_t nq, int32_t* cand_idx, float* cand_thr) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    unsigned char* a_s = smem;                              // 2 A tiles
+    unsigned char* b_s = smem + 2 * kTileBytes;             // kStages B tiles
+    float* sc = (float*)(b_s + kStages * kTileBytes);       // [kL][256] list scores
+    int32_t* ix = (int32_t*)(sc + kL * kRowsPerCta);        // [kL][256] list indices
+    TcBars* bars = (TcBars*)(ix + kL * kRowsPerCta);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int64_t nchunks = Mp / kTileRows;
+    const int64_t tile0 = (int64_t)blockIdx.x * 2;  // first of this CTA's two A tiles
+
+    if (tid == 0) {
+        mbar_init(&bars->a_full, 1);
+        for (int s = 0; s < kStages; ++s) mbar_init(&bars->full[s], 1), mbar_init(&bars->empty[s], 1);
+        for (int b = 0; b < 2; ++b) mbar_init(&bars->tmem_full[b], 1), mbar_init(&bars->tmem_empty[b], 8);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 9) {  // one warp allocates all 512 TMEM columns (1 CTA per SM: the shared-memory footprint forces it)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&bars->tmem_base))
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *(volatile uint32_t*)&bars->tmem_base;
+
+    if (warp == 8) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            mbar_expect_tx(&bars->a_full, 2 * kTileBytes);
+            tma_load_1d(a_s, aimg + tile0 * (kTileBytes / 4), 2 * kTileBytes, &bars->a_full);
+            for (int64_t c = 0; c < nchunks; ++c) {
+                const int st = (int)(c % kStages);
+                mbar_wait(&bars->empty[st], (uint32_t)(((c / kStages) & 1) ^ 1));
+                mbar_expect_tx(&bars->full[st], kTileBytes);
+                tma_load_1d(b_s + st * kTileBytes, bimg + c * (kTileBytes / 4), kTileBytes, &bars->full[st]);
+            }
+        }
+    } else if (warp == 9) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            mbar_wait(&bars->a_full, 0);
+            const uint32_t a_addr = smem_u32(a_s), b_addr = smem_u32(b_s);
+            // K-group pairs (A kg, B kg) of the 7 K=8 steps: hi.hi, hi.hi, lo.hi, lo.hi, hi.lo, hi.lo, ones.norm
+            const int akg[7] = {0, 2, 4, 6, 0, 2, 8};
+            const int bkg[7] = {0, 2, 0, 2, 4, 6, 8};
+            for (int64_t c = 0; c < nchunks; ++c) {
+                const int st = (int)(c % kStages), buf = (int)(c & 1);
+                mbar_wait(&bars->tmem_empty[buf], (uint32_t)(((c >> 1) & 1) ^ 1));
+                mbar_wait(&bars->full[st], (uint32_t)((c / kStages) & 1));
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+                for (int a = 0; a < 2; ++a) {
+                    const uint32_t d_tmem = tmem_base + (uint32_t)((buf * 2 + a) * 128);
+#pragma unroll
+                    for (int k = 0; k < 7; ++k)
+                        umma_tf32(d_tmem, umma_desc(a_addr + a * kTileBytes + akg[k] * kLBO),
+                                  umma_desc(b_addr + st * kTileBytes + bkg[k] * kLBO), k > 0 ? 1u : 0u);
+                }
+                umma_commit(&bars->empty[st]);        // smem stage reusable once these MMAs have read it
+                umma_commit(&bars->tmem_full[buf]);   // accumulators of this chunk complete
+            }
+        }
+    } else {
+        // ===== epilogue: thread = query row =====
+        const int a = warp >> 2;  // which A tile; warp%4 selects the TMEM lane quarter this warp may read
+        const int row = a * 128 + (warp & 3) * 32 + lane;  // row inside the CTA
+        float thr = __uint_as_float(F32_INF_BITS);
+        int maxpos = 0;
+        for (int l = 0; l < kL; ++l) {
+            sc[l * kRowsPerCta + row] = __uint_as_float(F32_INF_BITS);
+            ix[l * kRowsPerCta + row] = -1;
+        }
+        auto insert = [&](float s, int32_t cidx) {
+            sc[maxpos * kRowsPerCta + row] = s;
+            ix[maxpos * kRowsPerCta + row] = cidx;
+            float m = sc[row];
+            int mp = 0;
+#pragma unroll 8
+            for (int l = 1; l < kL; ++l) {
+                const float v = sc[l * kRowsPerCta + row];
+                if (v > m) m = v, mp = l;
+            }
+            thr = m;
+            maxpos = mp;
+        };
+        for (int64_t c = 0; c < nchunks; ++c) {
+            const int buf = (int)(c & 1);
+            mbar_wait(&bars->tmem_full[buf], (uint32_t)((c >> 1) & 1));
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((buf * 2 + a) * 128);
+            const int32_t c0 = (int32_t)(c * kTileRows);
+#pragma unroll 1
+            for (int part = 0; part < 4; ++part) {
+                float v[32];
+                tmem_ld32(taddr + part * 32, v);
+                float m = v[0];
+#pragma unroll
+                for (int i = 1; i < 32; ++i) m = fminf(m, v[i]);
+                if (m < thr) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (v[i] < thr) insert(v[i], c0 + part * 32 + i);
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars->tmem_empty[buf]);
+        }
+        const int64_t q = (int64_t)blockIdx.x * kRowsPerCta + row;
+        if (q < nq) {
+            for (int l = 0; l < kL; ++l) cand_idx[q * kL + l] = ix[l * kRowsPerCta + row];
+            cand_thr[q] = thr;
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 9) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+    }
+}
+
+}  // namespace
+
+int64_t knn_tc_padded_candidates(int64_t M) { return align_up(M, kTileRows); }
+int64_t knn_tc_padded_queries(int64_t nq) { return align_up(nq, kRowsPerCta); }
+int64_t knn_tc_image_floats(int64_t rows_padded) { return rows_padded * kRowFloats; }
+
+int knn_filter_tc(const float* z, int64_t M, int d, int64_t q_lo, int64_t nq, float* bimg, float* aimg,
+                  unsigned int* max_nrm_bits, int32_t* cand_idx, float* cand_thr, cudaStream_t st) {
+    if (d > 16) {
+        geocb_set_error("knn_filter_tc supports d <= 16");
+        return GEOCB_ERR_UNSUPPORTED;
+    }
+    const int64_t Mp = knn_tc_padded_candidates(M), nqp = knn_tc_padded_queries(nq);
+    const int64_t threads = (Mp + nqp) * kKGroups;
+    knn_tc_prep_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(z, M, d, Mp, q_lo, nq, nqp, bimg, aimg,
+                                                                           max_nrm_bits);
+    KERNEL_CHECK();
+    const size_t smem = (size_t)(2 + kStages) * kTileBytes + (size_t)kL * kRowsPerCta * 8 + sizeof(TcBars) + 64;
+    CU_TRY(cudaFuncSetAttribute(knn_filter_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    knn_filter_tc_kernel<<<(unsigned)(nqp / kRowsPerCta), kThreads, smem, st>>>(aimg, bimg, Mp, nq, cand_idx, cand_thr);
+    KERNEL_CHECK();
+    return 0;
+}
