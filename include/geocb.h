@@ -75,6 +75,16 @@ int geocb_edge_len_scatter(const float* ja, const float* jb, int64_t E, int P, i
                            const int64_t* pos_ij, const int64_t* pos_ji, float* len_out, float* data,
                            void* stream);
 
+/* BatchNorm2d(train) forward-mode JVP fused with the following ReLU, in place (part of the JVP stack behind
+ * riemannian_metric.py:12-35; the reference CLI keeps the decoder in train mode, build_codebook.py:27-29).
+ * x, t [rows][C*HW] f32 primal / tangent; statistics per group of rows_per_group consecutive rows (one reference
+ * batch of edges) and channel; pre_bias[C*HW] (nullable) is added to x first (bias of the preceding linear map);
+ * weight/bias [C] nullable (no affine); relu != 0 applies max(y,0) and masks the tangent.
+ * Supported: HW in {1,2,4,8,16}, (C*HW) % 16 == 0, rows % rows_per_group == 0, rows_per_group <= 512;
+ * otherwise GEOCB_ERR_UNSUPPORTED (the caller then composes the same formulas from library ops). */
+int geocb_bn_relu_jvp(float* x, float* t, int64_t rows, int C, int HW, int rows_per_group, const float* pre_bias,
+                      const float* weight, const float* bias, float eps, int relu, void* stream);
+
 /* --------------------------------------------- connected components ------
  * replaces scipy.sparse.csgraph.connected_components (knn_graph_optimized.py:175).
  * labels[n] = smallest vertex id of the component (undirected: the CSR must be

@@ -1,0 +1,190 @@
+// bn_jvp.cu -- BatchNorm2d (train mode) forward-mode JVP fused with the following ReLU, in place.
+//
+// Part of the Riemannian edge-length stage (reference: src/geo/riemannian_metric.py:12-35 differentiates
+// sigmoid(decoder(z)) with torch.autograd.functional.jvp; the reference CLI leaves the decoder in train mode,
+// build_codebook.py:27-29, so BatchNorm normalises with the statistics of each 512-edge batch and the JVP
+// differentiates through them).  For a batch ("group") of R rows and channel c with HW positions:
+//     mu = mean(x)  var = mean((x-mu)^2)  r = 1/sqrt(var+eps)  xh = (x-mu) r
+//     y  = xh w + b                         ty = w r ( t - mean(t) - xh mean(xh t) )
+//     ReLU: ty = y > 0 ? ty : 0 ; y = max(y, 0)
+// The PyTorch formulation makes ~14 passes over the (rows, C*HW) activations; this kernel reads x and t once and
+// writes them once.  One CTA = one group x one 16-float column slab (16/HW channels): HBM-bound, 16 B per float.
+#include "common.cuh"
+
+namespace {
+constexpr int kBnThreads = 256;
+
+template <int NRED>
+__device__ __forceinline__ void block_sum(float (&v)[NRED], float* s_red /* [8][NRED] */) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < NRED; ++i)
+#pragma unroll
+        for (int o = 16; o; o >>= 1) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
+    __syncthreads();  // previous use of s_red is over
+    if (lane == 0)
+#pragma unroll
+        for (int i = 0; i < NRED; ++i) s_red[warp * NRED + i] = v[i];
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < NRED; ++i) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < kBnThreads / 32; ++w) s += s_red[w * NRED + i];
+        v[i] = s;
+    }
+}
+
+// RPT rows per thread, CPB channels per slab (HW = 16 / CPB)
+template <int RPT, int CPB>
+__global__ void __launch_bounds__(kBnThreads) bn_relu_jvp_kernel(float* __restrict__ x, float* __restrict__ t, int R,
+                                                                 int ld, const float* __restrict__ pre_bias,
+                                                                 const float* __restrict__ weight,
+                                                                 const float* __restrict__ bias, float eps, int relu) {
+    constexpr int HW = 16 / CPB;
+    __shared__ float s_red[(kBnThreads / 32) * 2 * CPB];
+    const int col0 = blockIdx.x * 16;
+    const int64_t row0 = (int64_t)blockIdx.y * R;
+    float xv[RPT][16], tv[RPT][16];
+    float pb[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) pb[i] = pre_bias ? pre_bias[col0 + i] : 0.f;
+#pragma unroll
+    for (int k = 0; k < RPT; ++k) {
+        const int r = threadIdx.x + k * kBnThreads;
+        if (r < R) {
+            const float4* px = (const float4*)(x + (row0 + r) * ld + col0);
+            const float4* pt = (const float4*)(t + (row0 + r) * ld + col0);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float4 a = px[q], b = pt[q];
+                xv[k][4 * q] = a.x + pb[4 * q], xv[k][4 * q + 1] = a.y + pb[4 * q + 1];
+                xv[k][4 * q + 2] = a.z + pb[4 * q + 2], xv[k][4 * q + 3] = a.w + pb[4 * q + 3];
+                tv[k][4 * q] = b.x, tv[k][4 * q + 1] = b.y, tv[k][4 * q + 2] = b.z, tv[k][4 * q + 3] = b.w;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) xv[k][i] = 0.f, tv[k][i] = 0.f;
+        }
+    }
+    const float inv_cnt = 1.0f / (float)((int64_t)R * HW);
+    // ---- mean ----
+    float acc[2 * CPB];
+#pragma unroll
+    for (int c = 0; c < CPB; ++c) {
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < RPT; ++k)
+#pragma unroll
+            for (int h = 0; h < HW; ++h) s += xv[k][c * HW + h];
+        acc[c] = s;
+        acc[CPB + c] = 0.f;
+    }
+    block_sum<2 * CPB>(acc, s_red);
+    float mu[CPB];
+#pragma unroll
+    for (int c = 0; c < CPB; ++c) mu[c] = acc[c] * inv_cnt;
+    // ---- biased variance of the centred values ----
+#pragma unroll
+    for (int c = 0; c < CPB; ++c) {
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < RPT; ++k) {
+            const bool live = threadIdx.x + k * kBnThreads < R;
+#pragma unroll
+            for (int h = 0; h < HW; ++h) {
+                const float d = xv[k][c * HW + h] - mu[c];
+                xv[k][c * HW + h] = d;
+                s += live ? d * d : 0.f;
+            }
+        }
+        acc[c] = s;
+        acc[CPB + c] = 0.f;
+    }
+    block_sum<2 * CPB>(acc, s_red);
+    float rinv[CPB];
+#pragma unroll
+    for (int c = 0; c < CPB; ++c) rinv[c] = 1.0f / sqrtf(acc[c] * inv_cnt + eps);
+    // ---- tangent moments: mean(t), mean(xh t) ----
+#pragma unroll
+    for (int c = 0; c < CPB; ++c) {
+        float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+        for (int k = 0; k < RPT; ++k)
+#pragma unroll
+            for (int h = 0; h < HW; ++h) {
+                const float xh = xv[k][c * HW + h] * rinv[c];
+                xv[k][c * HW + h] = xh;
+                s0 += tv[k][c * HW + h];
+                s1 += xh * tv[k][c * HW + h];
+            }
+        acc[c] = s0;
+        acc[CPB + c] = s1;
+    }
+    block_sum<2 * CPB>(acc, s_red);
+    // ---- normalise, affine, ReLU, write back ----
+#pragma unroll
+    for (int k = 0; k < RPT; ++k) {
+        const int r = threadIdx.x + k * kBnThreads;
+        if (r >= R) continue;
+        float ox[16], ot[16];
+#pragma unroll
+        for (int c = 0; c < CPB; ++c) {
+            const int ch = blockIdx.x * CPB + c;
+            const float w = weight ? weight[ch] : 1.f, b = bias ? bias[ch] : 0.f;
+            const float mt = acc[c] * inv_cnt, m2 = acc[CPB + c] * inv_cnt;
+#pragma unroll
+            for (int h = 0; h < HW; ++h) {
+                const float xh = xv[k][c * HW + h];
+                float y = xh * w + b;
+                float ty = (rinv[c] * ((tv[k][c * HW + h] - mt) - xh * m2)) * w;
+                if (relu) {
+                    ty = y > 0.f ? ty : 0.f;
+                    y = fmaxf(y, 0.f);
+                }
+                ox[c * HW + h] = y;
+                ot[c * HW + h] = ty;
+            }
+        }
+        float4* px = (float4*)(x + (row0 + r) * ld + col0);
+        float4* pt = (float4*)(t + (row0 + r) * ld + col0);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            px[q] = make_float4(ox[4 * q], ox[4 * q + 1], ox[4 * q + 2], ox[4 * q + 3]);
+            pt[q] = make_float4(ot[4 * q], ot[4 * q + 1], ot[4 * q + 2], ot[4 * q + 3]);
+        }
+    }
+}
+
+template <int RPT>
+int launch_bn(int cpb, dim3 grid, cudaStream_t st, float* x, float* t, int R, int ld, const float* pre_bias,
+              const float* weight, const float* bias, float eps, int relu) {
+    switch (cpb) {
+        case 1: bn_relu_jvp_kernel<RPT, 1><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu); break;
+        case 2: bn_relu_jvp_kernel<RPT, 2><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu); break;
+        case 4: bn_relu_jvp_kernel<RPT, 4><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu); break;
+        case 8: bn_relu_jvp_kernel<RPT, 8><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu); break;
+        case 16: bn_relu_jvp_kernel<RPT, 16><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu); break;
+        default: return GEOCB_ERR_UNSUPPORTED;
+    }
+    KERNEL_CHECK();
+    return 0;
+}
+}  // namespace
+
+GEOCB_API int geocb_bn_relu_jvp(float* x, float* t, int64_t rows, int C, int HW, int rows_per_group,
+                                const float* pre_bias, const float* weight, const float* bias, float eps, int relu,
+                                void* stream) {
+    ARG_CHECK(x && t && rows > 0 && C > 0 && HW > 0 && rows_per_group > 0);
+    if (!(HW == 1 || HW == 2 || HW == 4 || HW == 8 || HW == 16) || (C * HW) % 16 != 0 || rows % rows_per_group != 0 ||
+        rows_per_group > 2 * kBnThreads || rows / rows_per_group > 65535) {
+        geocb_set_error("bn_relu_jvp: unsupported shape (C=%d HW=%d rows=%lld group=%d)", C, HW, (long long)rows,
+                        rows_per_group);
+        return GEOCB_ERR_UNSUPPORTED;
+    }
+    const dim3 grid((unsigned)(C * HW / 16), (unsigned)(rows / rows_per_group));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int cpb = 16 / HW, ld = C * HW;
+    if (rows_per_group <= kBnThreads) return launch_bn<1>(cpb, grid, st, x, t, rows_per_group, ld, pre_bias, weight, bias, eps, relu);
+    return launch_bn<2>(cpb, grid, st, x, t, rows_per_group, ld, pre_bias, weight, bias, eps, relu);
+}

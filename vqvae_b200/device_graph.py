@@ -118,6 +118,19 @@ def edge_len_scatter(ja, jb, e_lo, pos_ij, pos_ji, len_out, data):
                                      stream_ptr()), "edge_len_scatter")
 
 
+def bn_relu_jvp(x, t, C_, HW, rows_per_group, pre_bias, weight, bias, eps, relu):
+    """In-place fused BatchNorm(train) JVP (+ReLU) on primal x / tangent t, both [rows, C*HW] contiguous f32.
+    Returns False when the shape is outside what the kernel supports (caller falls back to library ops)."""
+    lib = _lib.load()
+    rows = x.shape[0]
+    if not (HW in (1, 2, 4, 8, 16) and (C_ * HW) % 16 == 0 and rows % rows_per_group == 0 and rows_per_group <= 512
+            and rows // rows_per_group <= 65535 and x.is_contiguous() and t.is_contiguous()):
+        return False
+    check(lib.geocb_bn_relu_jvp(ptr(x), ptr(t), rows, C_, HW, rows_per_group, ptr(pre_bias), ptr(weight), ptr(bias),
+                                float(eps), int(relu), stream_ptr()), "bn_relu_jvp")
+    return True
+
+
 # ------------------------------------------------------------ components / LCC
 def component_labels(g: DeviceCSR):
     lib = _lib.load()

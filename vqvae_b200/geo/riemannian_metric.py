@@ -177,24 +177,48 @@ def _unrolled_ops(layers, latent_dim):
 
 
 def _forward_mode(ops, z, dz, groups):
-    """Tangent of sigmoid(decoder(z)) along dz for rows z (R,C); returns (R,P)."""
+    """Tangent of sigmoid(decoder(z)) along dz for rows z (R,C); returns (R,P).
+    lin -> BatchNorm(train) -> ReLU runs as one GEMM + one fused in-place kernel (`geocb_bn_relu_jvp`)."""
     x, t = z, dz
     n = z.shape[0]
-    for op in ops:
+    pending_bias = None  # bias of the last linear map, folded into the fused BN kernel when one follows
+    i = 0
+    while i < len(ops):
+        op = ops[i]
         if op[0] == "lin":
             y = torch.cat([x, t], 0) @ op[1]  # primal and tangent share one GEMM
             x, t = y[:n], y[n:]
-            if op[2] is not None:
-                x = x + op[2]
+            pending_bias = op[2]
+            nxt = ops[i + 1] if i + 1 < len(ops) else None
+            fusable = (nxt is not None and nxt[0] == "bn" and (nxt[1].training or nxt[1].running_mean is None)
+                       and n % groups == 0)
+            if not fusable and pending_bias is not None:
+                x = x + pending_bias
+                pending_bias = None
         elif op[0] == "bn":
-            x4, t4 = _bn_pair(op[1], x.view(n, *op[2]), t.view(n, *op[2]), groups)
-            x, t = x4.reshape(n, -1), t4.reshape(n, -1)
+            m, shape = op[1], op[2]
+            relu_next = i + 1 < len(ops) and ops[i + 1][0] == "relu"
+            done = False
+            if (m.training or m.running_mean is None) and n % groups == 0:
+                done = dg.bn_relu_jvp(x, t, shape[0], shape[1] * shape[2], n // groups, pending_bias, m.weight, m.bias,
+                                      m.eps, relu_next)
+            if done:
+                pending_bias = None
+                if relu_next:
+                    i += 1
+            else:
+                if pending_bias is not None:
+                    x = x + pending_bias
+                    pending_bias = None
+                x4, t4 = _bn_pair(m, x.reshape(n, *shape), t.reshape(n, *shape), groups)
+                x, t = x4.reshape(n, -1), t4.reshape(n, -1)
         elif op[0] == "gn":
-            x4, t4 = _gn_pair(op[1], x.view(n, *op[2]), t.view(n, *op[2]))
+            x4, t4 = _gn_pair(op[1], x.reshape(n, *op[2]), t.reshape(n, *op[2]))
             x, t = x4.reshape(n, -1), t4.reshape(n, -1)
         else:
             t = t * (x > 0)
             x = torch.relu(x)
+        i += 1
     s = torch.sigmoid(x)  # always applied (:29)
     return s * (1 - s) * t
 
