@@ -125,7 +125,7 @@ int64_t geocb_sssp_workspace_bytes(int64_t n, int slots);
  *   out_d32[S,n] f32 (+inf unreachable); out_pred[S,n] int32 or NULL
  *   (predecessor = lowest-index neighbour u with fl(d[u]+w)==d[v]; -9999 for the
  *   source and unreachable vertices, scipy's convention).
- * delta > 0 (callers pass the mean edge weight).  Syncs.  stats_host (nullable):
+ * delta > 0 is the bucket width (callers pass 4x the mean edge weight; any value gives the same result).  Syncs.  stats_host (nullable):
  * int64[4] = {edge relaxations, rounds, threshold scans, improvements}.
  * Returns GEOCB_ERR_OVERFLOW if the kernel hit its round limit (8n+4096) without converging. */
 int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t n, const int32_t* sources, int S,

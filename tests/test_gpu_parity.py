@@ -179,6 +179,21 @@ def test_sssp_c1_graph_vs_oracle(geo, c1, slots):
     D, st = dg.sssp_multi(g, src, slots=slots, stats=True)
     assert np.array_equal(D.cpu().numpy(), oracle.sssp_multi(W, src))
     assert st["relaxations"] < 3 * 11 * (W.nnz + 20000)  # near-far keeps redundant work small
+    if slots == 3:
+        # sources stream through the slots (11 sources, 3 slots): predecessors are taken at each hand-over,
+        # a repeated source is an independent search, and a second call on the reused workspace is clean
+        src2 = np.r_[src[:5], src[:2]]
+        D2, P2 = dg.sssp_multi(g, src2, slots=3, want_pred=True)
+        D2, P2 = D2.cpu().numpy(), P2.cpu().numpy()
+        ref = oracle.sssp_multi(W, src2)
+        assert np.array_equal(D2, ref)
+        D64 = sparse.csgraph.dijkstra(W, directed=False, indices=src2)
+        Wc = W.tocsr()
+        for r in range(len(src2)):
+            v = np.nonzero(P2[r] >= 0)[0]
+            assert len(v) == 20000 - 1 - int(np.isinf(ref[r]).sum()) and P2[r][src2[r]] == -9999
+            w = np.asarray(Wc[P2[r][v], v]).ravel().astype(np.float64)
+            assert np.array_equal(D64[r][P2[r][v]] + w, D64[r][v])
 
 
 def test_sssp_c1_golden_digest(geo, c1, s1):

@@ -1,5 +1,5 @@
 """SSSP-only driver for timing / ncu: kNN graph of synthetic latents with hash weights (no JVP stage).
-usage: prof_sssp.py IMAGES SLOTS[,SLOTS..] [LAUNCHES] [--trace]   (latents = IMAGES*49)
+usage: prof_sssp.py IMAGES SLOTS[,SLOTS..] [LAUNCHES] [--trace] [--sources S]   (latents = IMAGES*49)
 The graph is cached under /tmp so several library builds can be compared in one gpurun call."""
 import os, sys, time
 from pathlib import Path
@@ -9,7 +9,11 @@ sys.path.insert(0, str(ROOT))
 from vqvae_b200 import _lib, device_graph as dg
 from vqvae_b200.geo.knn_graph_optimized import knn_graph_device
 
-args = [a for a in sys.argv[1:] if not a.startswith("--")]
+S_total = 0
+argv = sys.argv[1:]
+if "--sources" in argv:  # stream this many sources through the slots (default: sources = slots)
+    i = argv.index("--sources"); S_total = int(argv[i + 1]); del argv[i:i + 2]
+args = [a for a in argv if not a.startswith("--")]
 images, slot_list = int(args[0]), [int(x) for x in args[1].split(",")]
 launches = int(args[2]) if len(args) > 2 else 3
 trace = "--trace" in sys.argv
@@ -39,7 +43,8 @@ for slots in slot_list:
     rng = np.random.RandomState(0)
     times = []
     for i in range(launches):
-        src = rng.choice(g.n, slots, replace=False)
+        S = S_total or slots
+        src = rng.choice(g.n, S, replace=False)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         try:
@@ -52,13 +57,14 @@ for slots in slot_list:
     if not times:
         continue
     ms = float(np.median(times[1:] or times))
-    print(f"{tag} n={g.n} nnz={g.nnz} slots={slots}: {ms:.3f} ms  {slots*g.nnz/ms/1e6:.2f} G edge-relax/s  "
-          f"roofline {slots*16*(g.nnz+g.n)/ms/1e6/6538.9:.3f}  rounds={st['rounds']} scans={st['scans']} "
-          f"relax/edge={st['relaxations']/(slots*g.nnz):.3f} graph_s={t_graph:.1f}", flush=True)
+    print(f"{tag} n={g.n} nnz={g.nnz} slots={slots} sources={S}: {ms:.3f} ms  {S*g.nnz/ms/1e6:.2f} G edge-relax/s  "
+          f"roofline {S*16*(g.nnz+g.n)/ms/1e6/6538.9:.3f}  rounds={st['rounds']} scans={st['scans']} "
+          f"relax/edge={st['relaxations']/(S*g.nnz):.3f} graph_s={t_graph:.1f}", flush=True)
     if trace:
         # round trace of the last launch (written by the kernel into the tail of its workspace)
         total = _lib.load().geocb_sssp_workspace_bytes(g.n, slots)
         tr = [v for k, v in dg._ws_cache.items() if k[0] == "sssp"][0][total - 2048:total].view(torch.int64).cpu().numpy()
         nr = int(tr[7]); t = tr[8:8 + 2 * min(nr, 120):2]; q = tr[9:9 + 2 * min(nr, 120):2]
         ts = np.r_[t, tr[6]]
+        print(f"improvements/relax={st['improvements']/max(st['relaxations'],1):.4f}")
         print("round: popped -> us   " + "  ".join(f"{i}:{int(q[i])}->{(ts[i+1]-ts[i])/1e3:.0f}" for i in range(len(t))), flush=True)

@@ -5,6 +5,7 @@ Everything here works on torch CUDA tensors; the reference-facing modules in
 """
 from __future__ import annotations
 
+import os
 import ctypes as C
 
 import numpy as np
@@ -196,7 +197,9 @@ def sssp_multi(g: DeviceCSR, sources, unweighted=False, want_pred=False, delta=N
     src = torch.as_tensor(np.asarray(sources, dtype=np.int32), device=dev)
     S = int(src.numel())
     if delta is None:
-        delta = mean_w if mean_w > 0 else 1.0
+        # bucket width = 4 x mean edge weight: measured best on the 2.94M-vertex geodesic graph (1x: 110, 2x: 117,
+        # 4x: 120, 6x: 117, 10x: 117 G edge-relax/s; relaxations per edge 1.03 -> 1.06, rounds per source batch 19 -> 13)
+        delta = (mean_w if mean_w > 0 else 1.0) * float(os.environ.get("GEOCB_SSSP_DELTA_SCALE", "4"))
     slots = default_slots(g.n) if slots is None else slots
     slots = max(1, min(slots, S, 32))
     nbytes = lib.geocb_sssp_workspace_bytes(g.n, slots)
