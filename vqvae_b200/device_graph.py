@@ -215,6 +215,53 @@ def sssp_multi(g: DeviceCSR, sources, unweighted=False, want_pred=False, delta=N
     return res
 
 
+def sssp_multi_to_host(g: DeviceCSR, sources, out_host: torch.Tensor, unweighted=False, delta=None, slots=None,
+                       pred_host: torch.Tensor | None = None):
+    """S independent SSSPs whose (S,n) float32 result (and int32 predecessors) land in HOST tensors.
+
+    The sources run in lock-step batches of `slots`; the device->host copy of batch i is issued on a side stream and
+    overlaps the kernel of batch i+1 (two device staging buffers).  `out_host` should be pinned for the copy to be
+    asynchronous; pageable memory works but serialises.  Returns out_host (and pred_host)."""
+    dev = g.indptr.device
+    src = np.asarray(sources, dtype=np.int32)
+    S = int(src.size)
+    slots = default_slots(g.n) if slots is None else slots
+    slots = max(1, min(slots, S, 32))
+    assert out_host.shape == (S, g.n) and out_host.dtype == torch.float32 and out_host.device.type == "cpu"
+    main = torch.cuda.current_stream(dev)
+    side = _side_stream(dev)
+    bufs = [torch.empty((slots, g.n), dtype=torch.float32, device=dev) for _ in range(2)]
+    free = [None, None]  # event: the copy out of bufs[i] has finished
+    for bi, b0 in enumerate(range(0, S, slots)):
+        b1 = min(S, b0 + slots)
+        buf = bufs[bi & 1][:b1 - b0]
+        if free[bi & 1] is not None:
+            main.wait_event(free[bi & 1])
+        res = sssp_multi(g, src[b0:b1], unweighted=unweighted, want_pred=pred_host is not None, delta=delta,
+                         slots=slots, out=buf)
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            out_host[b0:b1].copy_(buf, non_blocking=True)
+            if pred_host is not None:
+                pred_host[b0:b1].copy_(res[1], non_blocking=True)
+                res[1].record_stream(side)
+            ev = torch.cuda.Event()
+            ev.record(side)
+        free[bi & 1] = ev
+    side.synchronize()
+    return (out_host, pred_host) if pred_host is not None else out_host
+
+
+_side_streams = {}
+
+
+def _side_stream(dev):
+    key = torch.device(dev).index if torch.device(dev).index is not None else torch.cuda.current_device()
+    if key not in _side_streams:
+        _side_streams[key] = torch.cuda.Stream(device=dev)
+    return _side_streams[key]
+
+
 class VoronoiState:
     """Running (dmin64, dmin32, label) over the inserted centres -- see geocb_voronoi_insert."""
 

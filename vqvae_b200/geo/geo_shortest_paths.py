@@ -10,6 +10,7 @@ from __future__ import annotations
 from typing import Tuple
 
 import numpy as np
+import torch
 from scipy import sparse
 
 from .. import _lib
@@ -67,11 +68,13 @@ def dijkstra_multi_source(W: sparse.spmatrix, sources, directed: bool = False, u
         if return_predecessors:
             return D, np.full((len(src), g.n), -9999, dtype=np.int32)
         return D
-    out = dg.sssp_multi(g, src, unweighted=use_unit, want_pred=return_predecessors)
+    # device->host copies of one batch of sources overlap the next batch's kernel (dg.sssp_multi_to_host)
+    D = torch.empty((len(src), g.n), dtype=torch.float32)
+    P = torch.empty((len(src), g.n), dtype=torch.int32) if return_predecessors else None
+    dg.sssp_multi_to_host(g, src, D, unweighted=use_unit, pred_host=P)
     if return_predecessors:
-        D, P = out
-        return D.cpu().numpy().astype(dtype, copy=False), P.cpu().numpy().astype(np.int32, copy=False)  # :42
-    return out.cpu().numpy().astype(dtype, copy=False)  # :50
+        return D.numpy().astype(dtype, copy=False), P.numpy()  # :42
+    return D.numpy().astype(dtype, copy=False)  # :50
 
 
 def dijkstra_single_source(W: sparse.spmatrix, source: int, directed: bool = False, unweighted: bool = False,

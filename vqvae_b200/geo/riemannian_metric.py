@@ -182,12 +182,14 @@ def _forward_mode(ops, z, dz, groups):
     x, t = z, dz
     n = z.shape[0]
     pending_bias = None  # bias of the last linear map, folded into the fused BN kernel when one follows
+    stacked = None       # buffer whose halves x and t currently are (the fused BN kernel works in place on it)
     i = 0
     while i < len(ops):
         op = ops[i]
         if op[0] == "lin":
-            y = torch.cat([x, t], 0) @ op[1]  # primal and tangent share one GEMM
+            y = (stacked if stacked is not None else torch.cat([x, t], 0)) @ op[1]  # primal and tangent share one GEMM
             x, t = y[:n], y[n:]
+            stacked = y
             pending_bias = op[2]
             nxt = ops[i + 1] if i + 1 < len(ops) else None
             fusable = (nxt is not None and nxt[0] == "bn" and (nxt[1].training or nxt[1].running_mean is None)
@@ -195,6 +197,7 @@ def _forward_mode(ops, z, dz, groups):
             if not fusable and pending_bias is not None:
                 x = x + pending_bias
                 pending_bias = None
+                stacked = None
         elif op[0] == "bn":
             m, shape = op[1], op[2]
             relu_next = i + 1 < len(ops) and ops[i + 1][0] == "relu"
@@ -212,12 +215,15 @@ def _forward_mode(ops, z, dz, groups):
                     pending_bias = None
                 x4, t4 = _bn_pair(m, x.reshape(n, *shape), t.reshape(n, *shape), groups)
                 x, t = x4.reshape(n, -1), t4.reshape(n, -1)
+                stacked = None
         elif op[0] == "gn":
             x4, t4 = _gn_pair(op[1], x.reshape(n, *op[2]), t.reshape(n, *op[2]))
             x, t = x4.reshape(n, -1), t4.reshape(n, -1)
+            stacked = None
         else:
             t = t * (x > 0)
             x = torch.relu(x)
+            stacked = None
         i += 1
     s = torch.sigmoid(x)  # always applied (:29)
     return s * (1 - s) * t
