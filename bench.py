@@ -153,6 +153,7 @@ def run_b200(a):
     from vqvae_b200.models import SpatialVAE
     from vqvae_b200.pipeline import build_codebook_device
 
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout to the one JSON line
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -166,6 +167,11 @@ def run_b200(a):
     z4 = torch.randn(a.images, 16, a.grid, a.grid, generator=torch.Generator().manual_seed(42))
     torch.manual_seed(0)
     decoder = SpatialVAE(**FASHION_CFG).decoder.to(dev)
+    if world > 1:  # NCCL connects lazily per protocol: take that out of the build seconds (process start-up, not work)
+        for nel in (1 << 10, 1 << 24):
+            w_in = torch.zeros(nel, dtype=torch.float32, device=dev)
+            dist.all_gather([torch.empty_like(w_in) for _ in range(world)], w_in)
+        del w_in
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     res = build_codebook_device(z4, decoder, k=20, sym="union", K=a.K, init="kpp", seed=42, batch_size=512,

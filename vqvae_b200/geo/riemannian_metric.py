@@ -141,6 +141,53 @@ def _gn_pair(m, x, t):
     return xh, th
 
 
+def _unique_taps(m):
+    """True when every (input position, output position) pair is linked by at most one kernel tap, i.e. the dense
+    matrix entries are single weights (always the case for dilation 1)."""
+    return tuple(m.dilation) == (1, 1)
+
+
+def _conv_matrix(m, shape):
+    """Dense (C*H*W, C'*H'*W') matrix of the linear map a Conv2d / ConvTranspose2d applies to a (C,H,W) input, built
+    by index arithmetic: every entry is exactly one kernel weight or 0 (no cuDNN call, whose first use costs each
+    process ~1 s of library initialisation).  Returns (A, out_shape) or None for grouped convolutions."""
+    if m.groups != 1 or any(isinstance(p, str) for p in (m.padding if isinstance(m.padding, tuple) else (m.padding,))):
+        return None
+    C, H, W = shape
+    w = m.weight
+    (sh, sw), (ph, pw), (dh, dw) = m.stride, m.padding, m.dilation
+    kh_n, kw_n = w.shape[2], w.shape[3]
+    transposed = isinstance(m, nn.ConvTranspose2d)
+    if transposed:
+        oph, opw = m.output_padding
+        Co = w.shape[1]
+        Ho = (H - 1) * sh - 2 * ph + dh * (kh_n - 1) + oph + 1
+        Wo = (W - 1) * sw - 2 * pw + dw * (kw_n - 1) + opw + 1
+    else:
+        Co = w.shape[0]
+        Ho = (H + 2 * ph - dh * (kh_n - 1) - 1) // sh + 1
+        Wo = (W + 2 * pw - dw * (kw_n - 1) - 1) // sw + 1
+    A = torch.zeros(C, H, W, Co, Ho, Wo, device=w.device, dtype=w.dtype)
+    for kh in range(kh_n):
+        for kw in range(kw_n):
+            if transposed:  # out[oh,ow] += in[ih,iw] * w[ci,co,kh,kw],  oh = ih*s - p + kh*d
+                ih = torch.arange(H)
+                iw = torch.arange(W)
+                oh, ow = ih * sh - ph + kh * dh, iw * sw - pw + kw * dw
+                wk = w[:, :, kh, kw]  # (C, Co)
+            else:           # out[oh,ow] += in[oh*s - p + kh*d, ...] * w[co,ci,kh,kw]
+                oh = torch.arange(Ho)
+                ow = torch.arange(Wo)
+                ih, iw = oh * sh - ph + kh * dh, ow * sw - pw + kw * dw
+                wk = w[:, :, kh, kw].t()  # (C, Co)
+            vh = (ih >= 0) & (ih < H) & (oh >= 0) & (oh < Ho)
+            vw = (iw >= 0) & (iw < W) & (ow >= 0) & (ow < Wo)
+            for a, b in zip(ih[vh].tolist(), oh[vh].tolist()):
+                for c, d in zip(iw[vw].tolist(), ow[vw].tolist()):
+                    A[:, a, c, :, b, d] = wk  # (dilation 1: one tap per (input position, output position) pair)
+    return A.reshape(C * H * W, Co * Ho * Wo).contiguous(), (Co, Ho, Wo)
+
+
 def _unrolled_ops(layers, latent_dim):
     """Decoder on a 1x1 latent grid as dense operators: every conv / transposed conv becomes the matrix of
     the linear map it applies to its (C,H,W) input (obtained by pushing an identity basis through the layer
@@ -149,14 +196,19 @@ def _unrolled_ops(layers, latent_dim):
     for m in layers:
         if isinstance(m, (nn.Conv2d, nn.ConvTranspose2d)):
             k = shape[0] * shape[1] * shape[2]
-            eye = torch.eye(k, device=m.weight.device, dtype=m.weight.dtype).view(k, *shape)
-            if isinstance(m, nn.Conv2d):
-                out = F.conv2d(eye, m.weight, None, m.stride, m.padding, m.dilation, m.groups)
+            direct = _conv_matrix(m, shape) if _unique_taps(m) else None
+            if direct is not None:
+                A, oshape = direct
             else:
-                out = F.conv_transpose2d(eye, m.weight, None, m.stride, m.padding, m.output_padding, m.groups, m.dilation)
-            oshape = tuple(out.shape[1:])
+                eye = torch.eye(k, device=m.weight.device, dtype=m.weight.dtype).view(k, *shape)
+                if isinstance(m, nn.Conv2d):
+                    out = F.conv2d(eye, m.weight, None, m.stride, m.padding, m.dilation, m.groups)
+                else:
+                    out = F.conv_transpose2d(eye, m.weight, None, m.stride, m.padding, m.output_padding, m.groups,
+                                             m.dilation)
+                oshape = tuple(out.shape[1:])
+                A = out.reshape(k, -1).contiguous()
             bias = None if m.bias is None else m.bias.view(-1, 1, 1).expand(oshape).reshape(-1).contiguous()
-            A = out.reshape(k, -1).contiguous()
             if ops and ops[-1][0] == "lin":
                 # two linear maps in a row (conv_in -> first ConvT): compose once, in fp64, round once
                 _, A0, b0, _ = ops.pop()

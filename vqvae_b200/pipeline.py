@@ -105,6 +105,7 @@ def build_codebook_device(z4: torch.Tensor, decoder, k=20, sym="union", K=512, i
     else:
         lo, hi = shard_range(M, rank, world)
         idx, dst, _ = dg.knn_topk(z_flat, k_eff + 1, lo, hi)
+        tm("knn_gather")
         idx = all_gather_rows(idx, M, world, rank, group, dist)
         dst = all_gather_rows(dst, M, world, rank, group, dist)
         me = torch.arange(M, device=dev, dtype=torch.int32)
@@ -130,6 +131,7 @@ def build_codebook_device(z4: torch.Tensor, decoder, k=20, sym="union", K=512, i
     else:
         lo, hi = shard_range(E, rank, world, multiple=batch_size)
         Lp = edge_lengths_device(decoder, z_flat, ei, ej, batch_size, e_lo=lo, e_hi=hi)
+        tm("edge_gather")
         L = all_gather_rows(Lp, E, world, rank, group, dist, multiple=batch_size)
         g_geo.data[pos_ij] = L
         g_geo.data[pos_ji] = L
