@@ -153,7 +153,11 @@ def run_b200(a):
     from vqvae_b200.models import SpatialVAE
     from vqvae_b200.pipeline import build_codebook_device
 
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout to the one JSON line
+    # keep stdout to the one JSON line: libraries (NCCL's version banner) print to fd 1, so fd 1 is pointed at
+    # stderr for the run and the line is written to the saved descriptor at the end
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -309,7 +313,8 @@ def run_b200(a):
                       "medoids_head": [int(x) for x in res.medoids[:5]]},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": n_launch, "clocks": clocks,
             "sssp_stats": {k_: int(v) for k_, v in stats_tot.items()}}
-    print(json.dumps(line), flush=True)
+    sys.stdout.flush()
+    os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
 

@@ -1,0 +1,95 @@
+"""Host-side logic that needs no GPU: decoder unrolling (conv -> dense matrix), shard arithmetic, CLI surface."""
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+
+
+def _by_identity(m, shape):
+    k = shape[0] * shape[1] * shape[2]
+    eye = torch.eye(k).view(k, *shape)
+    if isinstance(m, nn.ConvTranspose2d):
+        out = F.conv_transpose2d(eye, m.weight, None, m.stride, m.padding, m.output_padding, m.groups, m.dilation)
+    else:
+        out = F.conv2d(eye, m.weight, None, m.stride, m.padding, m.dilation, m.groups)
+    return out.reshape(k, -1), tuple(out.shape[1:])
+
+
+@pytest.mark.parametrize("make,shape", [
+    (lambda: nn.Conv2d(16, 32, 3, 1, 1), (16, 1, 1)),                                  # conv_in on a 1x1 latent cell
+    (lambda: nn.ConvTranspose2d(32, 16, 3, 2, 1, output_padding=1), (32, 1, 1)),       # reference decoder up-blocks
+    (lambda: nn.ConvTranspose2d(8, 4, 3, 2, 1, output_padding=1), (8, 2, 2)),
+    (lambda: nn.ConvTranspose2d(8, 4, 4, 2, 1), (8, 2, 2)),
+    (lambda: nn.ConvTranspose2d(6, 3, 3, 1, 1), (6, 4, 4)),
+    (lambda: nn.Conv2d(4, 6, 3, 2, 1), (4, 5, 5)),
+    (lambda: nn.Conv2d(4, 6, 1), (4, 3, 3)),
+    (lambda: nn.Conv2d(3, 5, (3, 2), (2, 1), (1, 0)), (3, 6, 4)),
+])
+def test_conv_matrix_entries_are_the_kernel_weights(make, shape):
+    """The dense operator built by index arithmetic equals, bit for bit, the one obtained by pushing an identity
+    basis through the layer (what reference-style autograd would differentiate: riemannian_metric.py:12-35)."""
+    from vqvae_b200.geo.riemannian_metric import _conv_matrix
+    torch.manual_seed(0)
+    m = make()
+    with torch.no_grad():
+        A, osh = _conv_matrix(m, shape)
+        R, rsh = _by_identity(m, shape)
+    assert osh == rsh and torch.equal(A, R)
+    # every non-zero entry is one of the layer's weights
+    assert set(A[A != 0].tolist()) <= set(m.weight.detach().reshape(-1).tolist())
+
+
+def test_conv_matrix_declines_what_it_cannot_express():
+    from vqvae_b200.geo.riemannian_metric import _conv_matrix, _unique_taps
+    assert _conv_matrix(nn.Conv2d(4, 4, 3, 1, 1, groups=2), (4, 3, 3)) is None
+    assert not _unique_taps(nn.Conv2d(4, 4, 3, 1, 2, dilation=2))
+    assert _unique_taps(nn.ConvTranspose2d(4, 4, 3, 2, 1))
+
+
+def test_unrolled_decoder_matches_module_forward():
+    """lin/bn/relu program of the FashionMNIST-shape decoder reproduces decoder(z) on a 1x1 grid (eval-mode BN so a
+    CPU forward is deterministic): same composition the GPU JVP path runs."""
+    import bench
+    from vqvae_b200.models import SpatialVAE
+    from vqvae_b200.geo import riemannian_metric as rm
+    torch.manual_seed(0)
+    dec = SpatialVAE(**bench.FASHION_CFG).decoder.eval()
+    for mod in dec.modules():
+        if isinstance(mod, nn.BatchNorm2d):
+            mod.running_mean.normal_(0, 0.1)
+            mod.running_var.uniform_(0.5, 1.5)
+    z = torch.randn(7, 16)
+    with torch.no_grad():
+        want = dec(z.view(7, 16, 1, 1)).reshape(7, -1)
+        ops = rm._unrolled_ops(rm._flatten_layers(dec), 16)
+        x = z
+        for op in ops:
+            if op[0] == "lin":
+                x = x @ op[1] + (0 if op[2] is None else op[2])
+            elif op[0] == "bn":
+                m, shape = op[1], op[2]
+                x = F.batch_norm(x.view(-1, *shape), m.running_mean, m.running_var, m.weight, m.bias, False, 0.0,
+                                 m.eps).reshape(x.shape[0], -1)
+            elif op[0] == "relu":
+                x = torch.relu(x)
+    assert x.shape == want.shape
+    assert torch.allclose(x, want, rtol=1e-5, atol=1e-6)
+
+
+def test_shard_ranges_keep_whole_bn_batches():
+    from vqvae_b200.pipeline import shard_range
+    E, bs = 46_400_123, 512
+    for world in (1, 2, 3, 4, 8):
+        cuts = [shard_range(E, r, world, multiple=bs) for r in range(world)]
+        assert cuts[0][0] == 0 and cuts[-1][1] == E
+        assert all(a[1] == b[0] for a, b in zip(cuts, cuts[1:]))
+        assert all(lo % bs == 0 for lo, _ in cuts)
+        sizes = [hi - lo for lo, hi in cuts]
+        assert max(sizes) - min(sizes) < 2 * bs  # one unit of imbalance + the ragged tail
