@@ -69,6 +69,25 @@ def test_knn_vs_oracle_shapes(geo, d, k):
     np.testing.assert_allclose(W.data, Wo.data, rtol=1e-6)
 
 
+def test_knn_cosine_vs_sklearn(geo):
+    """metric="cosine" (SURVEY 8f-2): same neighbour lists as sklearn's brute cosine search up to float32 near-ties
+    (sklearn ranks by a float32 GEMM, here by the exact order of the unit rows), distances within 2e-6 absolute."""
+    rs = np.random.RandomState(5)
+    z = rs.randn(3000, 16).astype(np.float32)
+    W, info = geo["knn"].build_knn_graph(z, k=10, metric="cosine", mode="distance", sym="union")
+    Wo, io = oracle.knn_graph(z, k=10, metric="cosine", mode="distance", sym="union")
+    assert info["indices"].shape == (3000, 10) and info["distances"].dtype == np.float32
+    same_rows = (info["indices"] == io["indices"]).all(axis=1)
+    assert same_rows.mean() > 0.995
+    same_sets = np.array([set(a) == set(b) for a, b in zip(info["indices"], io["indices"])])
+    assert same_sets.mean() > 0.998
+    assert np.abs(info["distances"][same_rows] - io["distances"][same_rows]).max() < 2e-6
+    assert W.shape == Wo.shape and abs(W.nnz - Wo.nnz) <= 0.005 * Wo.nnz
+    assert (W != W.T).nnz == 0 and W.diagonal().sum() == 0
+    with pytest.raises(ValueError):
+        geo["knn"].build_knn_graph(z, k=10, metric="manhattan")
+
+
 def test_knn_edge_cases(geo):
     # reference tests/test_knn_graph.py:11-42
     k = geo["knn"]

@@ -22,17 +22,40 @@ def _empty(n):
     return sparse.csr_matrix((n, n), dtype=np.float32)
 
 
-def knn_graph_device(z_dev: torch.Tensor, k: int, mode: str = "distance", sym: str = "mutual"):
+def _cosine_rows(z_dev: torch.Tensor) -> torch.Tensor:
+    """Rows scaled to unit length the way sklearn's cosine_distances does (float32 norms, zero rows left zero).
+    For unit rows |a-b|^2 = 2 - 2 a.b, so the exact Euclidean top-k of these rows IS the cosine top-k."""
+    nrm = torch.sqrt((z_dev * z_dev).sum(1))
+    nrm = torch.where(nrm == 0, torch.ones_like(nrm), nrm)
+    return (z_dev / nrm[:, None]).contiguous()
+
+
+def knn_graph_device(z_dev: torch.Tensor, k: int, mode: str = "distance", sym: str = "mutual",
+                     metric: str = "euclidean"):
     """Device-side body shared by every public builder.
 
     z_dev: (N,D) float32 CUDA tensor, N >= 2, 1 <= k <= N-1.
     Returns (DeviceCSR, nbr_idx int32 (N,k), nbr_dist f32 (N,k)), self already dropped
     following knn_graph_optimized.py:44-52.
+    metric "cosine" (reference :86-97 / sklearn metric="cosine"): neighbours are the exact Euclidean
+    top-k of the unit-length rows, reported distance = 1 - cosine similarity (fp64 dot, clipped to [0,2], f32).
+    A zero row has cosine distance 1 to everything; among all-tied candidates the lowest indices are returned.
     """
     if sym not in ("mutual", "union"):
         raise ValueError(f"Invalid symmetry mode: {sym}")  # :64
     N = z_dev.shape[0]
-    idx, dist, _ = dg.knn_topk(z_dev, k + 1)  # k+1 query incl. self (:39-42)
+    if metric == "cosine":
+        zn = _cosine_rows(z_dev)
+        idx, _, _ = dg.knn_topk(zn, k + 1)
+        dist = torch.empty(idx.shape, dtype=torch.float32, device=z_dev.device)
+        for lo in range(0, N, 1 << 18):  # bounded temporaries (fp64 gathered neighbours)
+            sl = slice(lo, min(N, lo + (1 << 18)))
+            dots = torch.einsum("nd,nkd->nk", zn[sl].double(), zn[idx[sl].long()].double())
+            dist[sl] = (1.0 - dots).clamp_(0.0, 2.0).float()
+    elif metric == "euclidean":
+        idx, dist, _ = dg.knn_topk(z_dev, k + 1)  # k+1 query incl. self (:39-42)
+    else:
+        raise ValueError(f"metric '{metric}' not supported. Use 'euclidean' or 'cosine'.")  # :99
     me = torch.arange(N, device=z_dev.device, dtype=torch.int32)
     if bool((idx[:, 0] == me).all()):  # :45-46
         idx, dist = idx[:, 1:].contiguous(), dist[:, 1:].contiguous()
@@ -53,13 +76,13 @@ def _build(z: np.ndarray, k: int, metric: str, mode: str, sym: str):
     k_eff = max(0, min(k, N - 1))  # :34
     if k_eff == 0:  # :35-37
         return _empty(N), {"distances": np.empty((N, 0), np.float32), "indices": np.empty((N, 0), dtype=int)}
-    if metric != "euclidean":
-        raise ValueError(f"metric '{metric}' not supported by the CUDA path (euclidean only)")
+    if metric not in ("euclidean", "cosine"):
+        raise ValueError(f"metric '{metric}' not supported. Use 'euclidean' or 'cosine'.")  # :99
     if sym not in ("mutual", "union"):
         raise ValueError(f"Invalid symmetry mode: {sym}")
     dev = _lib.require_cuda()
     z_dev = torch.from_numpy(np.ascontiguousarray(z, dtype=np.float32)).to(dev)
-    g, idx, dist = knn_graph_device(z_dev, k_eff, mode, sym)
+    g, idx, dist = knn_graph_device(z_dev, k_eff, mode, sym, metric)
     info = {"distances": dist.cpu().numpy(), "indices": idx.cpu().numpy().astype(int)}
     return g.to_scipy(), info
 
