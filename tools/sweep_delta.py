@@ -1,5 +1,7 @@
-"""Bucket-width / slot sweep of the SSSP on the real C2 geodesic graph (built once, cached under /tmp).
-usage: sweep_delta.py [SCALES] [SLOTS]    e.g.  sweep_delta.py 0.5,1,2,4 16"""
+"""Bucket-width / slot / library-variant sweep of the SSSP on the real C2 geodesic graph (built once, cached under /tmp).
+usage: sweep_delta.py [SCALES] [SLOTS] [LIB.so ...]    e.g.  sweep_delta.py 0.5,1,2,4 16
+Extra arguments are alternative builds of libgeocb.so (compile-time knobs of sssp.cu); each is loaded in turn in the
+same process, after the default library."""
 import os, sys, time
 from pathlib import Path
 import numpy as np, torch
@@ -29,17 +31,26 @@ src = med.numpy()[:64]
 _, _, mean_w = g.adjacency(False)
 D = torch.empty((64, g.n), dtype=torch.float32, device=dev)
 ref = None
-for slots in slot_list:
+libs = [None] + [a for a in sys.argv[3:]]
+import ctypes
+from pathlib import Path as _P
+for lib_path in libs:
+  if lib_path is not None:
+    _lib._lib = None
+    _lib.LIB_PATH = _P(lib_path)
+    _lib.load()
+    print(f"--- {lib_path}", flush=True)
+  for slots in slot_list:
     for sc in scales:
-        ts = []
-        for it in range(3):
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            _, st = dg.sssp_multi(g, src, slots=slots, out=D, delta=mean_w * sc, stats=True)
-            e1.record(); torch.cuda.synchronize()
-            ts.append(e0.elapsed_time(e1))
-        ms = min(ts[1:])
-        chk = float(D[:4].double().sum())
-        ref = chk if ref is None else ref
-        print(f"slots={slots} delta={sc:g}x mean: {ms:.2f} ms  {64*g.nnz/ms/1e6:.1f} G edge-relax/s  rounds={st['rounds']} scans={st['scans']} "
-              f"relax/edge={st['relaxations']/(64*g.nnz):.3f} same={chk == ref}", flush=True)
+          ts = []
+          for it in range(3):
+              e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+              e0.record()
+              _, st = dg.sssp_multi(g, src, slots=slots, out=D, delta=mean_w * sc, stats=True)
+              e1.record(); torch.cuda.synchronize()
+              ts.append(e0.elapsed_time(e1))
+          ms = min(ts[1:])
+          chk = float(D[:4].double().sum())
+          ref = chk if ref is None else ref
+          print(f"slots={slots} delta={sc:g}x mean: {ms:.2f} ms  {64*g.nnz/ms/1e6:.1f} G edge-relax/s  rounds={st['rounds']} scans={st['scans']} "
+                f"relax/edge={st['relaxations']/(64*g.nnz):.3f} same={chk == ref}", flush=True)

@@ -25,7 +25,11 @@
 //            drops the (rare) spurious frontier bits of the float filter and stale far marks exactly.
 //   One persistent cooperative kernel runs all rounds of `slots` concurrent sources; rounds are separated by
 //   grid.sync.  A warp flattens the rows of its <=32 popped vertices into one edge range and walks it 128 edges
-//   per trip, the next trip's edge loads issued before this trip's gathers are consumed.
+//   per trip (positions interleaved across lanes, so each edge load instruction reads 32 consecutive pairs = 8
+//   sectors), the next trip's edge loads issued before this trip's gathers are consumed.
+//   What bounds it (ncu): the L1 tag stage -- a gather of 32 random addresses is 32 tag lookups, one
+//   per clock per SM, 291 G lookups/s chip-wide -- not DRAM bandwidth (42 % of peak) and not latency (16 to 24
+//   resident warps per SM give the same throughput).
 // HBM model: 8 B edge pair + 8 B distance per relaxation = 16*(nnz+n) algorithmic bytes per source.
 #include <stdlib.h>
 #include "common.cuh"
@@ -40,7 +44,6 @@ constexpr int kMaxSlots = 32;
 #define GEOCB_SSSP_MINBLOCKS 3
 #endif
 constexpr int kThreads = GEOCB_SSSP_THREADS;
-constexpr int kWarps = kThreads / 32;
 #ifndef GEOCB_SSSP_PER
 #define GEOCB_SSSP_PER 4
 #endif
@@ -140,39 +143,22 @@ __device__ __forceinline__ double ld_cg_f64(const double* p) {
     return __longlong_as_double((long long)ld_cg_u64((const u64*)p));
 }
 
-// owner lane (+1) of each of this lane's kPer flat positions tile+kPer*lane+k, given each lane's item [start,start+len)
-__device__ __forceinline__ void locate(uint32_t tile, uint32_t start, uint32_t len, uint32_t* own32, int wl, int j[kPer]) {
-    constexpr int kW = kPer / 4;  // marker words per lane (one byte per flat position)
-    __syncwarp();
+// Item (= lane index) owning each of this lane's kPer flat positions tile + 32*k + lane.  Positions are interleaved
+// across the warp so that one load instruction covers 32 consecutive edge pairs (8 sectors, not 32).  Each lane holds
+// one item [start, start+len); starts are non-decreasing, so the owner of p is the last lane whose start <= p (an
+// empty item shares its start with its successor and can never be that lane while p is inside the flattened range).
+__device__ __forceinline__ void locate(uint32_t tile, uint32_t start, int wl, int j[kPer]) {
 #pragma unroll
-    for (int w = 0; w < kW; ++w) own32[wl * kW + w] = 0;
-    __syncwarp();
-    if (len > 0 && start >= tile && start - tile < kTile) ((uint8_t*)own32)[start - tile] = (uint8_t)(wl + 1);
-    __syncwarp();
-    const unsigned before = __ballot_sync(0xffffffffu, len > 0 && start < tile);
-    const int carry = before ? 32 - __clz(before) : 0;
-    int m[kPer];
-    int run = 0;
+    for (int k = 0; k < kPer; ++k) j[k] = 0;
 #pragma unroll
-    for (int w = 0; w < kW; ++w) {
-        const uint32_t ow = own32[wl * kW + w];
+    for (int st = 16; st; st >>= 1) {
 #pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            run = max(run, (int)((ow >> (8 * b)) & 255u));
-            m[w * 4 + b] = run;
+        for (int k = 0; k < kPer; ++k) {
+            const int probe = min(j[k] + st, 31);
+            const uint32_t t = __shfl_sync(0xffffffffu, start, probe);
+            if (j[k] + st <= 31 && t <= tile + 32u * k + wl) j[k] += st;
         }
     }
-    int sc = run;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, sc, o);
-        if (wl >= o) sc = max(sc, t);
-    }
-    int ex = __shfl_up_sync(0xffffffffu, sc, 1);
-    if (wl == 0) ex = 0;
-    ex = max(ex, carry);
-#pragma unroll
-    for (int i = 0; i < kPer; ++i) j[i] = max(max(ex, m[i]) - 1, 0);
 }
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -185,12 +171,10 @@ __global__ void __launch_bounds__(kThreads, GEOCB_SSSP_MINBLOCKS) sssp_kernel(Ss
     const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
     const int64_t gwarp = gtid >> 5, nwarps = gthreads >> 5;
-    const int wlane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int wlane = threadIdx.x & 31;
     __shared__ double s_thr[kMaxSlots], s_hint[kMaxSlots];
     __shared__ int s_epoch[kMaxSlots], s_done[kMaxSlots], s_need[kMaxSlots];
     __shared__ int s_flag, s_alldone;
-    __shared__ uint32_t s_own[kWarps][kTile / 4];
-    uint32_t* own32 = s_own[wib];
     const uint64_t pol_keep = policy_evict_last();
     const uint64_t pol_stream = policy_evict_first();
 
@@ -334,10 +318,10 @@ __global__ void __launch_bounds__(kThreads, GEOCB_SSSP_MINBLOCKS) sssp_kernel(Ss
                 if (T == 0) continue;
                 int jj[kPer];
                 uint2 e[kPer];
-                locate(0, start, len, own32, wlane, jj);
+                locate(0, start, wlane, jj);
 #pragma unroll
                 for (int k = 0; k < kPer; ++k) {
-                    const uint32_t f = kPer * wlane + k;
+                    const uint32_t f = 32u * k + wlane;
                     const uint32_t off = __shfl_sync(0xffffffffu, rowoff, jj[k]);
                     e[k] = f < T ? ld_edge(p.adj + (uint32_t)(off + f), pol_stream) : pad_edge;
                 }
@@ -348,17 +332,18 @@ __global__ void __launch_bounds__(kThreads, GEOCB_SSSP_MINBLOCKS) sssp_kernel(Ss
                     for (int k = 0; k < kPer; ++k) duk[k] = __shfl_sync(0xffffffffu, du, jj[k]);
 #pragma unroll
                     for (int k = 0; k < kPer; ++k) ubv[k] = ld_ub(ub_s + e[k].x, pol_keep);
-                    n_relax += min((uint32_t)kPer, T - min(T, tile + kPer * wlane));
+#pragma unroll
+                    for (int k = 0; k < kPer; ++k) n_relax += tile + 32u * k + wlane < T;
                     // next trip's edge pairs are requested before this trip's gathers are consumed
                     uint2 en[kPer];
                     int jn[kPer];
 #pragma unroll
                     for (int k = 0; k < kPer; ++k) en[k] = pad_edge, jn[k] = 0;
                     if (tile + kTile < T) {
-                        locate(tile + kTile, start, len, own32, wlane, jn);
+                        locate(tile + kTile, start, wlane, jn);
 #pragma unroll
                         for (int k = 0; k < kPer; ++k) {
-                            const uint32_t f = tile + kTile + kPer * wlane + k;
+                            const uint32_t f = tile + kTile + 32u * k + wlane;
                             const uint32_t off = __shfl_sync(0xffffffffu, rowoff, jn[k]);
                             if (f < T) en[k] = ld_edge(p.adj + (uint32_t)(off + f), pol_stream);
                         }
