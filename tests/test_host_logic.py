@@ -93,3 +93,45 @@ def test_shard_ranges_keep_whole_bn_batches():
         assert all(lo % bs == 0 for lo, _ in cuts)
         sizes = [hi - lo for lo, hi in cuts]
         assert max(sizes) - min(sizes) < 2 * bs  # one unit of imbalance + the ragged tail
+
+
+def _run_py(code, extra_path=()):
+    import os
+    import subprocess
+    env = dict(os.environ)
+    env["PYTHONPATH"] = os.pathsep.join([str(ROOT), *map(str, extra_path)])
+    env.pop("VQVAE_REFERENCE_ROOT", None)
+    return subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+
+
+def test_src_shim_standalone():
+    """Without a reference checkout the shim exposes exactly this repo's modules."""
+    r = _run_py("import src, src.geo.knn_graph_optimized as k, src.scripts.build_codebook as b, src.models as m;"
+                "print(src.reference_src(), k.build_knn_graph.__module__, m.SpatialVAE.__module__)")
+    assert r.returncode == 0, r.stderr
+    assert r.stdout.split() == ["None", "vqvae_b200.geo.knn_graph_optimized", "vqvae_b200.models.spatial_vae"]
+
+
+@pytest.mark.skipif(not Path("/root/reference/src/training/build_codebook_legacy.py").exists(),
+                    reason="needs a checkout of the reference (not present on the GPU box)")
+def test_src_shim_overlays_reference_drivers():
+    """With the reference behind this repo on PYTHONPATH its legacy YAML drivers import unchanged and
+    bind the geodesic functions of this repo; modules this repo does not implement come from the reference."""
+    code = (
+        "import importlib, src\n"
+        "e = importlib.import_module('src.training.build_codebook_legacy')\n"
+        "r = importlib.import_module('src.training.build_riemannian_codebook_legacy')\n"
+        "from src.models import VAE, SpatialVAE\n"
+        "import src.scripts.build_codebook as cli, src.utils.spatial_latents as u\n"
+        "print(e.__file__, e.build_knn_graph_auto.__module__, e.fit_kmedoids_optimized.__module__,\n"
+        "      r.edge_lengths_riemannian.__module__, r.largest_connected_component.__module__, VAE.__module__,\n"
+        "      SpatialVAE.__module__, cli.__file__, u.__file__)\n")
+    r = _run_py(code, ["/root/reference"])
+    assert r.returncode == 0, r.stderr
+    out = r.stdout.split()
+    assert out[0] == "/root/reference/src/training/build_codebook_legacy.py"
+    assert out[1:5] == ["vqvae_b200.geo.knn_graph_optimized", "vqvae_b200.geo.kmeans_optimized",
+                        "vqvae_b200.geo.riemannian_metric", "vqvae_b200.geo.knn_graph_optimized"]
+    assert out[5] == "src.models.vae" and out[6] == "vqvae_b200.models.spatial_vae"
+    assert out[7] == str(ROOT / "src" / "scripts" / "build_codebook.py")
+    assert out[8] == "/root/reference/src/utils/spatial_latents.py"
