@@ -36,9 +36,12 @@ int geocb_device_info(int* sm_count, int* cc);
  * replaces sklearn NearestNeighbors.fit/kneighbors (knn_graph_optimized.py:39-42).
  * For query rows [q_lo,q_hi) of z[M,d] (row-major f32) find the kq nearest rows
  * of z (self included), ordered by (exact fp64 squared distance, index).
- *   pass 1: fused fp32 tiled  |b|^2 - 2ab  + per-thread top-(kq+slack) filter
+ *   pass 1: filter  |b|^2 - 2ab  over all candidates, keeping the best kq+slack per row:
+ *           d <= 16 and kq <= 26: tcgen05 tensor cores, 3xTF32 split (fp32-grade scores,
+ *           csrc/knn_tc.cu; env GEOCB_KNN_TC=0 disables); otherwise fused fp32 FFMA2 tiles.
  *   pass 2: exact fp64 re-rank of the candidates; rows whose filter margin is
  *           not provably safe are redone by an exact fp64 brute-force kernel.
+ *   The result never depends on which filter ran.
  * out_idx[(q_hi-q_lo),kq] int32, out_dist same shape f32 = sqrt(fp64 d2) (nullable).
  * n_unsafe (device int32[1], nullable): rows that took the exact brute-force path. */
 int geocb_knn_topk(const float* z, int64_t M, int d, int64_t q_lo, int64_t q_hi, int kq,
