@@ -1,6 +1,7 @@
 #!/bin/bash
 # default build and the GEOCB_SSSP_UB16 variant: SSSP / K-medoids / pipeline parity, then throughput on the C2 graph
-V=/root/repo/vqvae_b200/variants/libgeocb_ub16.so
+make -C vqvae_b200/csrc ub16 > /dev/null 2>&1
+V=$PWD/vqvae_b200/libgeocb_ub16.so
 python -c "import torch" 2>/dev/null
 timeout 200 python -m pytest tests -x -q -m gpu -k "sssp or kmedoids or pipeline" 2>&1 | tail -1
 GEOCB_LIB=$V timeout 200 python -m pytest tests -x -q -m gpu -k "sssp or kmedoids or pipeline" 2>&1 | tail -3
