@@ -135,3 +135,21 @@ def test_src_shim_overlays_reference_drivers():
     assert out[5] == "src.models.vae" and out[6] == "vqvae_b200.models.spatial_vae"
     assert out[7] == str(ROOT / "src" / "scripts" / "build_codebook.py")
     assert out[8] == "/root/reference/src/utils/spatial_latents.py"
+
+
+def test_tf32_split_helpers():
+    """The opt-in 3xTF32 GEMM helper: hi part has a 10-bit mantissa, hi+lo is exact, and on a backend without TF32
+    (CPU) the three-GEMM sum is x@w minus only the lo*lo term."""
+    from vqvae_b200.geo import riemannian_metric as rm
+    torch.manual_seed(0)
+    x = torch.randn(64, 512)
+    w = torch.randn(512, 96) / 22
+    xh = rm._tf32_round(x)
+    assert int((xh.view(torch.int32) & 0x1FFF).abs().max()) == 0
+    assert torch.equal(xh + (x - xh), x)
+    assert float(((x - xh).abs() / x.abs()).max()) <= 2.0 ** -11
+    ref = x.double() @ w.double()
+    err3 = float((rm._mm_split3(x, w).double() - ref).abs().max() / ref.abs().max())
+    err1 = float(((x @ w).double() - ref).abs().max() / ref.abs().max())
+    assert err3 < 4 * err1 + 1e-7
+    assert not rm._use_split3(512)  # off unless GEOCB_JVP_3XTF32=1
