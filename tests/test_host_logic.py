@@ -153,3 +153,28 @@ def test_tf32_split_helpers():
     err1 = float(((x @ w).double() - ref).abs().max() / ref.abs().max())
     assert err3 < 4 * err1 + 1e-7
     assert not rm._use_split3(512)  # off unless GEOCB_JVP_3XTF32=1
+
+
+def test_bench_reference_arm_contract():
+    """`bench.py --impl reference` (CPU, SciPy Dijkstra through the oracle) prints exactly one JSON line with the
+    contract's keys; the B200 arm refuses to run without a CUDA device instead of falling back."""
+    import json
+    import os
+    import subprocess
+    env = dict(os.environ, PYTHONPATH=str(ROOT))
+    r = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
+                        "--images", "80", "--ref-latents", "3000"], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    for key in ("impl", "metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better",
+                "scaling", "vs_baseline", "dtype", "data", "config", "cpu_baseline", "e2e"):
+        assert key in d, key
+    assert d["impl"] == "reference" and d["metric"] == "sssp_edge_relax_per_s" and d["unit"] == "edge-relax/s"
+    assert d["value"] > 0 and d["e2e"]["value"] == d["value"] and d["e2e"]["h2d_bytes_per_step"] == 0
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and "workload" in d["config"]
+    if not torch.cuda.is_available():
+        r2 = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--steps", "1", "--warmup", "0", "--images", "80"],
+                            env=env, capture_output=True, text=True, timeout=600)
+        assert r2.returncode != 0 and r2.stdout.strip() == ""
