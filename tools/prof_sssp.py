@@ -63,8 +63,15 @@ for slots in slot_list:
     if trace:
         # round trace of the last launch (written by the kernel into the tail of its workspace)
         total = _lib.load().geocb_sssp_workspace_bytes(g.n, slots)
-        tr = [v for k, v in dg._ws_cache.items() if k[0] == "sssp"][0][total - 2048:total].view(torch.int64).cpu().numpy()
+        phases = os.environ.get("PROF_PHASES") == "1"  # library built with -DGEOCB_SSSP_TRACE_PHASES (4096-byte stats)
+        sb = 4096 if phases else 2048
+        tr = [v for k, v in dg._ws_cache.items() if k[0] == "sssp"][0][total - sb:total].view(torch.int64).cpu().numpy()
         nr = int(tr[7]); t = tr[8:8 + 2 * min(nr, 120):2]; q = tr[9:9 + 2 * min(nr, 120):2]
         ts = np.r_[t, tr[6]]
         print(f"improvements/relax={st['improvements']/max(st['relaxations'],1):.4f}")
+        if phases:
+            nrr = min(nr, 120)
+            a_end, b_end = tr[256:256 + nrr], tr[384:384 + nrr]
+            print("round: sweep us + control/scan us   " + "  ".join(
+                f"{i}:{(a_end[i]-t[i])/1e3:.0f}+{(b_end[i]-a_end[i])/1e3:.0f}" for i in range(nrr)), flush=True)
         print("round: popped -> us   " + "  ".join(f"{i}:{int(q[i])}->{(ts[i+1]-ts[i])/1e3:.0f}" for i in range(len(t))), flush=True)

@@ -50,6 +50,13 @@ constexpr int kThreads = GEOCB_SSSP_THREADS;
 constexpr int kPer = GEOCB_SSSP_PER;  // edges (= independent ub gathers in flight) per lane per trip: 4 or 8
 constexpr int kTile = 32 * kPer;      // flat edges per warp trip
 typedef unsigned long long u64;
+// stats block at the end of the workspace: 4 counters + per-round (start time, popped) trace of the last launch;
+// GEOCB_SSSP_TRACE_PHASES (profiling builds only) adds per-round end-of-sweep / end-of-scan times at u64 [256+r], [384+r]
+#ifdef GEOCB_SSSP_TRACE_PHASES
+constexpr int kStatsBytes = 4096;
+#else
+constexpr int kStatsBytes = 2048;
+#endif
 
 #ifdef GEOCB_SSSP_UB16
 typedef uint16_t ub_t;  // bf16 bits
@@ -408,6 +415,13 @@ __global__ void __launch_bounds__(kThreads, GEOCB_SSSP_MINBLOCKS) sssp_kernel(Ss
         }
         grid.sync();
         ++n_rounds;
+#ifdef GEOCB_SSSP_TRACE_PHASES
+        if (p.stats && gtid == 0 && round < 120) {  // every block has finished its sweep
+            u64 t;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+            p.stats[256 + round] = t;
+        }
+#endif
         if (p.stats && round < 120) {
             popped = __reduce_add_sync(0xffffffffu, popped);
             if (wlane == 0 && popped) atomicAdd(p.stats + 9 + 2 * round, (u64)popped);
@@ -492,6 +506,13 @@ __global__ void __launch_bounds__(kThreads, GEOCB_SSSP_MINBLOCKS) sssp_kernel(Ss
             }
             __syncthreads();
         }
+#ifdef GEOCB_SSSP_TRACE_PHASES
+        if (p.stats && gtid == 0 && round < 120) {  // control + (if any slot ran dry) threshold scan done
+            u64 t;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+            p.stats[384 + round] = t;
+        }
+#endif
         // ---- termination test (uniform) ----
         if (threadIdx.x == 0) s_alldone = 1;
         __syncthreads();
@@ -598,7 +619,7 @@ WsLayout ws_layout(int64_t n, int slots, bool own_dist) {
     w.ctl = off;
     off += align_up((int64_t)kMaxSlots * sizeof(SlotCtl), 256);
     w.stats = off;
-    off += 2048;  // 4 counters + a (time, popped vertices) trace of the last launch's first 120 rounds
+    off += kStatsBytes;  // 4 counters + a (time, popped vertices) trace of the last launch's first 120 rounds
     w.total = off;
     return w;
 }
@@ -665,7 +686,7 @@ GEOCB_API int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t 
     int grid = 0;
     int rc = coop_grid(&grid);
     if (rc) return rc;
-    CU_TRY(cudaMemsetAsync(ws + w.stats, 0, 2048, st));
+    CU_TRY(cudaMemsetAsync(ws + w.stats, 0, kStatsBytes, st));
     for (int s0 = 0; s0 < S; s0 += slots) {
         SsspParams p;
         fill_params(p, w, ws, row_ptr, adj, n, delta);
@@ -675,7 +696,7 @@ GEOCB_API int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t 
         p.out_d32 = out_d32 + (int64_t)s0 * n;
         p.out_pred = out_pred ? out_pred + (int64_t)s0 * n : nullptr;
         p.voronoi = 0;
-        if (s0 + slots < S || s0 > 0) CU_TRY(cudaMemsetAsync(ws + w.stats + 64, 0, 2048 - 64, st));  // trace = last launch
+        if (s0 + slots < S || s0 > 0) CU_TRY(cudaMemsetAsync(ws + w.stats + 64, 0, kStatsBytes - 64, st));  // trace = last launch
         void* args[] = {&p};
         CU_TRY(cudaLaunchCooperativeKernel((void*)sssp_kernel, dim3(grid), dim3(kThreads), args, 0, st));
     }
@@ -699,7 +720,7 @@ GEOCB_API int geocb_voronoi_init(int64_t n, double* dmin64, float* dmin32, int32
         return GEOCB_ERR_WORKSPACE;
     }
     char* ws = (char*)workspace;
-    CU_TRY(cudaMemsetAsync(ws + w.stats, 0, 2048, (cudaStream_t)stream));
+    CU_TRY(cudaMemsetAsync(ws + w.stats, 0, kStatsBytes, (cudaStream_t)stream));
     voronoi_init_kernel<<<592, 256, 0, (cudaStream_t)stream>>>(
         n, w.nwords, (u64*)dmin64, dmin32, label, (u64*)(ws + w.proc), (ub_t*)(ws + w.ub), align_up(n, 4), (uint32_t*)(ws + w.inq0),
         (uint32_t*)(ws + w.inq1), (uint32_t*)(ws + w.dirty));
