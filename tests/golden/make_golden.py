@@ -11,6 +11,11 @@ Cases
   c1   : BASELINE.json configs[0] (1250x16x4x4 -> 20000 latents, k=20 union, K=512).
          Stored as digests + the small arrays (medoids, qe, degree stats, sampled
          weights/distances) because the full graph is several MB (c1_digest.npz).
+  c3   : CIFAR-shape case of BASELINE.json configs[2] at a CPU-runnable size (`--c3`): z = randn(1250,32,4,4;
+         seed 42) -> 20000 latents d=32, CIFAR spatial decoder (in_channels 3, output 32, latent_dim 32,
+         dec 256-128-64, BatchNorm train mode; configs/cifar10/spatial/geodesic/vae.yaml:36-44 and the CLI flags
+         of scripts/run_cifar10_spatial_geodesic_pipeline.py:63-71), JVP output P = 3x8x8 = 192, k=20 union,
+         K=512 kpp seed 42.  Stored like c1 (c3_digest.npz).
 The decoder weights are not stored: `decoder_sha` pins the state_dict produced by
 `torch.manual_seed(0); SpatialVAE(**FASHION_CFG)` so the GPU box can rebuild it.
 """
@@ -51,15 +56,19 @@ def state_sha(sd):
     return h.hexdigest()
 
 
-def make_decoder():
+CIFAR_CFG = dict(in_channels=3, output_image_size=32, latent_dim=32, enc_channels=[64, 128, 256],
+                 dec_channels=[256, 128, 64], recon_loss="mse", norm_type="batch", mse_use_sigmoid=False)
+
+
+def make_decoder(cfg=None):
     torch.manual_seed(0)
-    vae = SpatialVAE(**FASHION_CFG)  # train mode, as build_codebook.py:27-29 leaves it
+    vae = SpatialVAE(**(cfg or FASHION_CFG))  # train mode, as build_codebook.py:27-29 leaves it
     return vae.decoder
 
 
-def run_reference(z4, k, sym, K, seed=42, batch=512):
+def run_reference(z4, k, sym, K, seed=42, batch=512, cfg=None):
     """build_codebook.py:31-76 verbatim in behaviour, on in-memory inputs."""
-    dec = make_decoder()
+    dec = make_decoder(cfg)
     dsha = state_sha(dec.state_dict())
     N, C, H, Wd = z4.shape
     zf = z4.permute(0, 2, 3, 1).reshape(-1, C).numpy()
@@ -89,7 +98,10 @@ def run_reference(z4, k, sym, K, seed=42, batch=512):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--skip-c1", action="store_true")
+    ap.add_argument("--c3", action="store_true", help="only (re)generate c3_digest.npz")
     a = ap.parse_args()
+    if a.c3:
+        return make_c3()
 
     # ---------------- s1: full stage-boundary arrays ----------------
     z4 = torch.randn(125, 16, 4, 4, generator=torch.Generator().manual_seed(42))
@@ -159,6 +171,35 @@ def main():
         ref_seconds=np.array([r["tm"]["knn"], r["tm"]["edge_len"], r["tm"]["kmedoids"], total]),
     )
     print("c1:", "E", len(r["L"]), "nnz", Wl.nnz, "qe", r["qe"], "med[:5]", r["med"][:5], r["tm"], "total", total)
+
+
+def make_c3():
+    z4 = torch.randn(1250, 32, 4, 4, generator=torch.Generator().manual_seed(42))
+    t0 = time.perf_counter()
+    r = run_reference(z4, k=20, sym="union", K=512, cfg=CIFAR_CFG)
+    total = time.perf_counter() - t0
+    Wl = r["Wl"].tocsr()
+    Wl.sort_indices()
+    samp = np.linspace(0, len(r["L"]) - 1, 4096).astype(np.int64)
+    src = np.array([0, 19999, int(r["med"][0])], dtype=np.int64)
+    D = dijkstra_multi_source(Wl, src)
+    deg = np.diff(Wl.indptr)
+    np.savez_compressed(
+        HERE / "c3_digest.npz",
+        n=np.int64(Wl.shape[0]), nnz=np.int64(Wl.nnz), E=np.int64(len(r["L"])),
+        knn_idx_sha=np.array(sha(r["idx"].astype(np.int32))),
+        euc_indptr_sha=np.array(sha(r["We"].indptr.astype(np.int32))),
+        euc_indices_sha=np.array(sha(r["We"].indices.astype(np.int32))),
+        deg_min_mean_max=np.array([deg.min(), deg.mean(), deg.max()], dtype=np.float64),
+        edge_sample_pos=samp, edge_sample_len=r["L"][samp],
+        edge_len_min_mean_max=np.array([r["L"].min(), r["L"].mean(), r["L"].max()], dtype=np.float64),
+        lcc_size=np.int64(r["mask"].sum()), medoids=r["med"].astype(np.int64), qe=np.float64(r["qe"]),
+        codes_sha=np.array(sha(r["codes"].astype(np.int32))), sssp_src=src, sssp_D_sha=np.array(sha(D)),
+        sssp_D_sample=D[:, ::97].copy(), cluster_sizes=np.bincount(r["assign"], minlength=512).astype(np.int32),
+        decoder_sha=np.array(r["dsha"]), z_sha=np.array(sha(r["zf"])),
+        ref_seconds=np.array([r["tm"]["knn"], r["tm"]["edge_len"], r["tm"]["kmedoids"], total]),
+    )
+    print("c3:", "E", len(r["L"]), "nnz", Wl.nnz, "qe", r["qe"], "med[:5]", r["med"][:5], r["tm"], "total", total)
 
 
 if __name__ == "__main__":
