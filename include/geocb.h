@@ -135,6 +135,21 @@ int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t n, const i
                      double delta, int slots, void* workspace, int64_t workspace_bytes, float* out_d32,
                      int32_t* out_pred, int64_t* stats_host, void* stream);
 
+/* Source-vectorised variant of geocb_sssp_multi (csrc/sssp_vm.cu): same results bit for bit, different layout.
+ * The geocb_sssp_vm_slots() (=16) sources of a launch sit side by side per vertex (dist[v][16], ub[v][16], one
+ * frontier mask word per vertex); lane&15 = source, a half-warp = one edge, so an edge pair is loaded once and one
+ * coalesced 64-byte gather serves all 16 sources.  The vertex range is cut into B destination blocks so that the
+ * randomly accessed state of one block stays L2 resident: geocb_sssp_vm_blocks fills blk[(B+1)][n] (uint32 pair offset
+ * where row v enters block b; needs < 2^32 adjacency pairs, else GEOCB_ERR_UNSUPPORTED; syncs) once per graph.
+ * Rounds that pop fewer than blk_min_active vertices run unblocked.  No predecessors (use geocb_sssp_multi).
+ * stats_host (nullable): int64[8] = {relaxations, rounds, scans, improvements, edge visits, blocked rounds, -, -}. */
+int geocb_sssp_vm_slots(void);
+int64_t geocb_sssp_vm_workspace_bytes(int64_t n);
+int geocb_sssp_vm_blocks(const int64_t* row_ptr, const void* adj, int64_t n, int B, uint32_t* blk, void* stream);
+int geocb_sssp_multi_vm(const void* adj, const uint32_t* blk, int B, int64_t n, const int32_t* sources, int S,
+                        double delta, int64_t blk_min_active, void* workspace, int64_t workspace_bytes,
+                        float* out_d32, int64_t* stats_host, void* stream);
+
 /* ------------------------------------------- incremental Voronoi SSSP ----
  * The K-medoids path (kmeans_optimized.py:40-44, 97-100, 125-134) only ever uses
  * d_min[v] = min_k D[k,v], argmin_k and sum d_min^2, so instead of K full SSSPs the

@@ -62,6 +62,17 @@ class DeviceCSR:
             self._adj[key] = (row_ptr, adj, mean_w)
         return self._adj[key]
 
+    def vm_blocks(self, B, unit_weights=False):
+        """Destination-block entry offsets blk[(B+1)][n] of the adjacency rows (geocb_sssp_vm_blocks), cached."""
+        key = ("blk", bool(unit_weights), int(B))
+        if key not in self._adj:
+            lib = _lib.load()
+            row_ptr, adj, _ = self.adjacency(unit_weights)
+            blk = torch.empty((B + 1) * self.n, dtype=torch.int32, device=row_ptr.device)
+            check(lib.geocb_sssp_vm_blocks(ptr(row_ptr), ptr(adj), self.n, int(B), ptr(blk), stream_ptr()), "sssp_vm_blocks")
+            self._adj[key] = blk
+        return self._adj[key]
+
 
 # --------------------------------------------------------------------------- kNN
 def knn_topk(z, kq, q_lo=0, q_hi=None, want_dist=True):
@@ -188,14 +199,64 @@ def default_slots(n):
     return 16
 
 
+def vm_default_blocks(n):
+    """Destination blocks of the vertex-major kernel: 200 B of randomly accessed state per vertex (dist 128 + ub 64 +
+    masks 8), one block's share kept near 40 MB so that it stays L2 resident next to the streamed data."""
+    return int(os.environ.get("GEOCB_SSSP_VM_BLOCKS", max(1, min(64, -(-n * 200 // (40 << 20))))))
+
+
+def _pick_kernel(kernel, S, want_pred):
+    """'slot' = csrc/sssp.cu (one table per source), 'vm' = csrc/sssp_vm.cu (16 sources side by side per vertex).
+    'auto': vm for batches of sources wide enough to share edge loads and gathers; predecessors need 'slot'."""
+    kernel = kernel or os.environ.get("GEOCB_SSSP_KERNEL", "auto")
+    if kernel not in ("auto", "slot", "vm"):
+        raise ValueError(f"unknown SSSP kernel '{kernel}'")
+    if want_pred:
+        return "slot"
+    if kernel == "auto":
+        return "vm" if S >= VM_MIN_SOURCES else "slot"
+    return kernel
+
+
+VM_MIN_SOURCES = int(os.environ.get("GEOCB_SSSP_VM_MIN_SOURCES", "8"))
+
+
+def sssp_multi_vm(g: DeviceCSR, sources, unweighted=False, delta=None, out=None, stats=False, blocks=None,
+                  blk_min_active=None):
+    """S independent SSSPs through the vertex-major kernel -> D32[S,n] on the device."""
+    lib = _lib.load()
+    dev = g.indptr.device
+    row_ptr, adj, mean_w = g.adjacency(unweighted)
+    B = vm_default_blocks(g.n) if blocks is None else int(blocks)
+    blk = g.vm_blocks(B, unweighted)
+    src = torch.as_tensor(np.asarray(sources, dtype=np.int32), device=dev)
+    S = int(src.numel())
+    if delta is None:
+        delta = (mean_w if mean_w > 0 else 1.0) * float(os.environ.get("GEOCB_SSSP_VM_DELTA_SCALE", "4"))
+    if blk_min_active is None:
+        # a blocked round scans the n mask words B times; worth it once the popped rows' gathers would thrash L2
+        blk_min_active = int(os.environ.get("GEOCB_SSSP_VM_MIN_ACTIVE", max(1, g.n // 16)))
+    ws = _workspace("sssp_vm", lib.geocb_sssp_vm_workspace_bytes(g.n), dev)
+    D = out if out is not None else torch.empty((S, g.n), dtype=torch.float32, device=dev)
+    st = (C.c_int64 * 8)()
+    check(lib.geocb_sssp_multi_vm(ptr(adj), ptr(blk), B, g.n, ptr(src), S, float(delta), int(blk_min_active), ptr(ws),
+                                  ws.numel(), ptr(D), st, stream_ptr()), "sssp_multi_vm")
+    if stats:
+        return D, dict(relaxations=st[0], rounds=st[1], scans=st[2], improvements=st[3], edge_visits=st[4],
+                       blocked_rounds=st[5], slots=lib.geocb_sssp_vm_slots(), delta=delta, blocks=B, kernel="vm")
+    return D
+
+
 def sssp_multi(g: DeviceCSR, sources, unweighted=False, want_pred=False, delta=None, slots=None, out=None,
-               stats=False):
+               stats=False, kernel=None):
     """S independent SSSPs -> D32[S,n] (+pred int32[S,n]) on the device."""
     lib = _lib.load()
     dev = g.indptr.device
     row_ptr, adj, mean_w = g.adjacency(unweighted)
     src = torch.as_tensor(np.asarray(sources, dtype=np.int32), device=dev)
     S = int(src.numel())
+    if _pick_kernel(kernel, S, want_pred) == "vm":
+        return sssp_multi_vm(g, sources, unweighted=unweighted, delta=delta, out=out, stats=stats)
     if delta is None:
         # bucket width = 4 x mean edge weight: measured best on the 2.94M-vertex geodesic graph (1x: 110, 2x: 117,
         # 4x: 120, 6x: 117, 10x: 117 G edge-relax/s; relaxations per edge 1.03 -> 1.06, rounds per source batch 19 -> 13)
@@ -211,12 +272,13 @@ def sssp_multi(g: DeviceCSR, sources, unweighted=False, want_pred=False, delta=N
                                ptr(D), ptr(P), st, stream_ptr()), "sssp_multi")
     res = (D, P) if want_pred else D
     if stats:
-        return res, dict(relaxations=st[0], rounds=st[1], scans=st[2], improvements=st[3], slots=slots, delta=delta)
+        return res, dict(relaxations=st[0], rounds=st[1], scans=st[2], improvements=st[3], slots=slots, delta=delta,
+                         kernel="slot")
     return res
 
 
 def sssp_multi_to_host(g: DeviceCSR, sources, out_host: torch.Tensor, unweighted=False, delta=None, slots=None,
-                       pred_host: torch.Tensor | None = None):
+                       pred_host: torch.Tensor | None = None, kernel=None):
     """S independent SSSPs whose (S,n) float32 result (and int32 predecessors) land in HOST tensors.
 
     The sources run in lock-step batches of `slots`; the device->host copy of batch i is issued on a side stream and
@@ -227,6 +289,8 @@ def sssp_multi_to_host(g: DeviceCSR, sources, out_host: torch.Tensor, unweighted
     S = int(src.size)
     slots = default_slots(g.n) if slots is None else slots
     slots = max(1, min(slots, S, 32))
+    if _pick_kernel(kernel, S, pred_host is not None) == "vm":
+        slots = min(S, _lib.load().geocb_sssp_vm_slots())  # one launch per batch: the copy-out overlaps the next launch
     assert out_host.shape == (S, g.n) and out_host.dtype == torch.float32 and out_host.device.type == "cpu"
     main = torch.cuda.current_stream(dev)
     side = _side_stream(dev)
@@ -238,7 +302,7 @@ def sssp_multi_to_host(g: DeviceCSR, sources, out_host: torch.Tensor, unweighted
         if free[bi & 1] is not None:
             main.wait_event(free[bi & 1])
         res = sssp_multi(g, src[b0:b1], unweighted=unweighted, want_pred=pred_host is not None, delta=delta,
-                         slots=slots, out=buf)
+                         slots=slots, out=buf, kernel=kernel)
         side.wait_stream(main)
         with torch.cuda.stream(side):
             out_host[b0:b1].copy_(buf, non_blocking=True)
