@@ -105,12 +105,29 @@ int geocb_csr_compact_fill(const int64_t* indptr, const int32_t* indices, const 
                            const int32_t* new_id, int64_t n, const int64_t* out_indptr, int32_t* out_indices,
                            float* out_data, void* stream);
 
+/* ------------------------------------------ undirected view of a CSR ------
+ * replaces the host-side W.T / maximum / minimum passes that scipy's `directed=False` implies
+ * (csgraph.dijkstra at geo_shortest_paths.py:36-49, connected_components at knn_graph_optimized.py:175):
+ * an edge {i,j} exists when (i,j) or (j,i) is stored; its weight is the smaller stored value.
+ * geocb_csr_sym_check (rows sorted by column, no duplicates) returns in *flags_host (syncs):
+ *   1 = a negative weight (the reference raises ValueError, geo_shortest_paths.py:18-19),
+ *   2 = some (i,j) has no stored (j,i),  4 = (i,j) and (j,i) differ in weight,
+ * and fills extra[n] (int32) with the number of entries each row gains.  When flags & 6,
+ * _count (syncs) sizes and _fill writes the merged, column-sorted CSR. */
+int geocb_csr_sym_check(const int64_t* indptr, const int32_t* indices, const float* data, int64_t n, int32_t* extra,
+                        int* flags_host, void* stream);
+int geocb_csr_undirected_count(const int64_t* indptr, const int32_t* extra, int64_t n, int64_t* out_indptr,
+                               int64_t* nnz_host, void* stream);
+int geocb_csr_undirected_fill(const int64_t* indptr, const int32_t* indices, const float* data, int64_t n,
+                              const int64_t* out_indptr, int32_t* out_indices, float* out_data, void* stream);
+
 /* ----------------------------------------------------------- SSSP --------
  * Graph in "adjacency-pair" form: adj[row_ptr[v] .. row_ptr[v+1]) are 8-byte
  * (int32 col, f32 weight) pairs; every row is padded to an even count so rows
  * start 16-byte aligned (pad entries: col = v, weight = +inf).
  * geocb_adj_count / _fill build it from CSR (unit_weights != 0 -> all weights 1,
  * the reference's `unweighted=True`, geo_shortest_paths.py:31-33). */
+/* (GEOCB_ERR_UNSUPPORTED if the graph has >= 2^32 pairs: the kernels use 32-bit pair offsets) */
 int geocb_adj_count(const int64_t* indptr, int64_t n, int64_t* row_ptr, int64_t* n_pairs_host, void* stream);
 int geocb_adj_fill(const int64_t* indptr, const int32_t* indices, const float* data, int64_t n, int unit_weights,
                    const int64_t* row_ptr, void* adj, double* weight_sum /* device f64[1], nullable */, void* stream);
@@ -126,14 +143,17 @@ int64_t geocb_sssp_workspace_bytes(int64_t n, int slots);
  * Per relaxation the kernel gathers only a float32 upper bound of dist[v] (exact filter),
  * frontiers are bitmaps swept in vertex order (see csrc/sssp.cu).
  *   out_d32[S,n] f32 (+inf unreachable); out_pred[S,n] int32 or NULL
- *   (predecessor = lowest-index neighbour u with fl(d[u]+w)==d[v]; -9999 for the
- *   source and unreachable vertices, scipy's convention).
+ *   (predecessor = lowest-index u with an edge u->v and fl(d[u]+w)==d[v]; -9999 for the
+ *   source and unreachable vertices, scipy's convention).  Predecessors are found over v's
+ *   IN-edges: in_row_ptr / in_adj = adjacency pairs of the transposed graph for a directed
+ *   (asymmetric) graph, both NULL for a symmetric one.
  * delta > 0 is the bucket width (callers pass 4x the mean edge weight; any value gives the same result).  Syncs.  stats_host (nullable):
  * int64[4] = {edge relaxations, rounds, threshold scans, improvements}.
  * Returns GEOCB_ERR_OVERFLOW if the kernel hit its round limit (8n+4096) without converging. */
 int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t n, const int32_t* sources, int S,
                      double delta, int slots, void* workspace, int64_t workspace_bytes, float* out_d32,
-                     int32_t* out_pred, int64_t* stats_host, void* stream);
+                     int32_t* out_pred, const int64_t* in_row_ptr, const void* in_adj, int64_t* stats_host,
+                     void* stream);
 
 /* Source-vectorised variant of geocb_sssp_multi (csrc/sssp_vm.cu): same results bit for bit, different layout.
  * The geocb_sssp_vm_slots() (=16) sources of a launch sit side by side per vertex (dist[v][16], ub[v][16], one
@@ -166,6 +186,9 @@ int geocb_voronoi_init(int64_t n, double* dmin64, float* dmin32, int32_t* label,
 int geocb_voronoi_insert(const int64_t* row_ptr, const void* adj, int64_t n, int32_t center, int32_t code,
                          double delta, double* dmin64, float* dmin32, int32_t* label, void* workspace,
                          int64_t workspace_bytes, void* stream);
+/* inserts are asynchronous; this reads back whether any of them hit the round limit (8n+4096) without
+ * converging (GEOCB_ERR_OVERFLOW).  Syncs. */
+int geocb_voronoi_check(int64_t n, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------ k-means++ sampling -----
  * replaces kmeans_optimized.py:47-61: inf handling, probs = d_min_safe**2,

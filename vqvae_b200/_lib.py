@@ -36,10 +36,13 @@ SIGNATURES = {
     "geocb_lcc_mask": (_int, [_p, _i64, _p, _p, _pi64, _pi64, _p]),
     "geocb_csr_compact_count": (_int, [_p, _p, _p, _i64, _p, _pi64, _p]),
     "geocb_csr_compact_fill": (_int, [_p, _p, _p, _p, _p, _i64, _p, _p, _p, _p]),
+    "geocb_csr_sym_check": (_int, [_p, _p, _p, _i64, _p, C.POINTER(_int), _p]),
+    "geocb_csr_undirected_count": (_int, [_p, _p, _i64, _p, _pi64, _p]),
+    "geocb_csr_undirected_fill": (_int, [_p, _p, _p, _i64, _p, _p, _p, _p]),
     "geocb_adj_count": (_int, [_p, _i64, _p, _pi64, _p]),
     "geocb_adj_fill": (_int, [_p, _p, _p, _i64, _int, _p, _p, _p, _p]),
     "geocb_sssp_workspace_bytes": (_i64, [_i64, _int]),
-    "geocb_sssp_multi": (_int, [_p, _p, _i64, _p, _int, _f64, _int, _p, _i64, _p, _p, _pi64, _p]),
+    "geocb_sssp_multi": (_int, [_p, _p, _i64, _p, _int, _f64, _int, _p, _i64, _p, _p, _p, _p, _pi64, _p]),
     "geocb_sssp_vm_slots": (_int, []),
     "geocb_sssp_vm_workspace_bytes": (_i64, [_i64]),
     "geocb_sssp_vm_blocks": (_int, [_p, _p, _i64, _int, _p, _p]),
@@ -47,6 +50,7 @@ SIGNATURES = {
     "geocb_voronoi_workspace_bytes": (_i64, [_i64]),
     "geocb_voronoi_init": (_int, [_i64, _p, _p, _p, _p, _i64, _p]),
     "geocb_voronoi_insert": (_int, [_p, _p, _i64, _i32, _i32, _f64, _p, _p, _p, _p, _i64, _p]),
+    "geocb_voronoi_check": (_int, [_i64, _p, _i64, _p]),
     "geocb_pairwise_plan_size": (_i64, [_i64]),
     "geocb_pairwise_plan_host": (_int, [_i64, _pi64]),
     "geocb_kpp_workspace_bytes": (_i64, [_i64]),

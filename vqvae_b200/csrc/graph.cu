@@ -223,6 +223,62 @@ __global__ void compact_fill_kernel(const int64_t* indptr, const int32_t* col, c
     }
 }
 
+// ------------------------------------------- undirected view of a CSR graph ----
+// scipy's directed=False semantics (csgraph.dijkstra / connected_components): an edge {i,j} exists when either
+// (i,j) or (j,i) is stored and its weight is the smaller of the stored values.
+__device__ __forceinline__ int64_t find_col(const int32_t* col, int64_t b, int64_t e, int32_t key) {
+    const int64_t g = first_greater(col, b, e, key - 1);  // lower_bound(key)
+    return (g < e && col[g] == key) ? g : -1;
+}
+// flags: 1 = negative weight, 2 = some (i,j) without a stored (j,i), 4 = (i,j) and (j,i) stored with different weights;
+// extra[j] counts the entries row j gains.  One warp per row.
+__global__ void csr_sym_check_kernel(const int64_t* indptr, const int32_t* col, const float* val, int64_t n,
+                                     int32_t* extra, int* flags) {
+    const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (i >= n) return;
+    int f = 0;
+    for (int64_t p = indptr[i] + lane; p < indptr[i + 1]; p += 32) {
+        const int32_t j = col[p];
+        const float w = val[p];
+        if (w < 0.0f) f |= 1;
+        const int64_t q = find_col(col, indptr[j], indptr[j + 1], (int32_t)i);
+        if (q < 0) {
+            f |= 2;
+            atomicAdd(extra + j, 1);
+        } else if (val[q] != w) {
+            f |= 4;
+        }
+    }
+    f = __reduce_or_sync(0xffffffffu, f);
+    if (lane == 0 && f) atomicOr(flags, f);
+}
+__global__ void undirected_len_kernel(const int64_t* indptr, const int32_t* extra, int64_t n, int32_t* len) {
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < n) len[v] = (int32_t)(indptr[v + 1] - indptr[v]) + extra[v];
+}
+__global__ void undirected_fill_kernel(const int64_t* indptr, const int32_t* col, const float* val, int64_t n,
+                                       const int64_t* out_ptr, int32_t* cursor, int32_t* tmp_col, float* tmp_val) {
+    const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const int64_t b = indptr[i], o = out_ptr[i];
+    for (int64_t p = b + lane; p < indptr[i + 1]; p += 32) {
+        const int32_t j = col[p];
+        float w = val[p];
+        const int64_t q = find_col(col, indptr[j], indptr[j + 1], (int32_t)i);
+        if (q >= 0) {
+            w = fminf(w, val[q]);
+        } else {  // row j gains (j,i): appended behind its own entries, sorted into place afterwards
+            const int64_t slot = out_ptr[j] + (indptr[j + 1] - indptr[j]) + atomicAdd(cursor + j, 1);
+            tmp_col[slot] = (int32_t)i;
+            tmp_val[slot] = w;
+        }
+        tmp_col[o + (p - b)] = j;
+        tmp_val[o + (p - b)] = w;
+    }
+}
+
 struct TmpBuf {  // stream-ordered scratch
     void* p = nullptr;
     cudaStream_t st;
@@ -308,7 +364,12 @@ GEOCB_API int geocb_adj_count(const int64_t* indptr, int64_t n, int64_t* row_ptr
     adj_len_kernel<<<blocks_for(n), kT, 0, st>>>(indptr, n, (int32_t*)len.p);
     KERNEL_CHECK();
     if ((rc = scan_exclusive_i32((int32_t*)len.p, n, row_ptr, st))) return rc;
-    return read_i64(row_ptr + n, n_pairs_host, st);
+    if ((rc = read_i64(row_ptr + n, n_pairs_host, st))) return rc;
+    if (*n_pairs_host >= (1LL << 32)) {  // the SSSP kernels address (col, weight) pairs with 32-bit offsets
+        geocb_set_error("graph has %lld adjacency pairs (limit 2^32 - 1)", (long long)*n_pairs_host);
+        return GEOCB_ERR_UNSUPPORTED;
+    }
+    return 0;
 }
 
 GEOCB_API int geocb_adj_fill(const int64_t* indptr, const int32_t* indices, const float* data, int64_t n,
@@ -393,6 +454,55 @@ GEOCB_API int geocb_csr_compact_fill(const int64_t* indptr, const int32_t* indic
     ARG_CHECK(indptr && indices && data && mask && new_id && out_indptr && out_indices && out_data && n > 0);
     compact_fill_kernel<<<blocks_for(n * 32), kT, 0, (cudaStream_t)stream>>>(indptr, indices, data, mask, new_id, n,
                                                                               out_indptr, out_indices, out_data);
+    KERNEL_CHECK();
+    return 0;
+}
+
+GEOCB_API int geocb_csr_sym_check(const int64_t* indptr, const int32_t* indices, const float* data, int64_t n,
+                                  int32_t* extra, int* flags_host, void* stream) {
+    ARG_CHECK(indptr && indices && data && extra && flags_host && n > 0);
+    cudaStream_t st = (cudaStream_t)stream;
+    TmpBuf flags(st);
+    int rc = flags.alloc(4);
+    if (rc) return rc;
+    CU_TRY(cudaMemsetAsync(flags.p, 0, 4, st));
+    CU_TRY(cudaMemsetAsync(extra, 0, (size_t)n * 4, st));
+    csr_sym_check_kernel<<<blocks_for(n * 32), kT, 0, st>>>(indptr, indices, data, n, extra, (int*)flags.p);
+    KERNEL_CHECK();
+    CU_TRY(cudaMemcpyAsync(flags_host, flags.p, 4, cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    return 0;
+}
+
+GEOCB_API int geocb_csr_undirected_count(const int64_t* indptr, const int32_t* extra, int64_t n, int64_t* out_indptr,
+                                         int64_t* nnz_host, void* stream) {
+    ARG_CHECK(indptr && extra && out_indptr && nnz_host && n > 0);
+    cudaStream_t st = (cudaStream_t)stream;
+    TmpBuf len(st);
+    int rc = len.alloc((size_t)n * 4);
+    if (rc) return rc;
+    undirected_len_kernel<<<blocks_for(n), kT, 0, st>>>(indptr, extra, n, (int32_t*)len.p);
+    KERNEL_CHECK();
+    if ((rc = scan_exclusive_i32((int32_t*)len.p, n, out_indptr, st))) return rc;
+    return read_i64(out_indptr + n, nnz_host, st);
+}
+
+GEOCB_API int geocb_csr_undirected_fill(const int64_t* indptr, const int32_t* indices, const float* data, int64_t n,
+                                        const int64_t* out_indptr, int32_t* out_indices, float* out_data,
+                                        void* stream) {
+    ARG_CHECK(indptr && indices && data && out_indptr && out_indices && out_data && n > 0);
+    cudaStream_t st = (cudaStream_t)stream;
+    int64_t nnz = 0;
+    int rc = read_i64(out_indptr + n, &nnz, st);
+    if (rc) return rc;
+    TmpBuf cur(st), tcol(st), tval(st);
+    if ((rc = cur.alloc((size_t)n * 4)) || (rc = tcol.alloc((size_t)nnz * 4)) || (rc = tval.alloc((size_t)nnz * 4)))
+        return rc;
+    CU_TRY(cudaMemsetAsync(cur.p, 0, (size_t)n * 4, st));
+    undirected_fill_kernel<<<blocks_for(n * 32), kT, 0, st>>>(indptr, indices, data, n, out_indptr, (int32_t*)cur.p,
+                                                               (int32_t*)tcol.p, (float*)tval.p);
+    row_rank_sort<<<blocks_for(n * 32), kT, 0, st>>>(out_indptr, n, (int32_t*)tcol.p, (float*)tval.p, out_indices,
+                                                      out_data);
     KERNEL_CHECK();
     return 0;
 }

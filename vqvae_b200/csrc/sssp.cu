@@ -93,7 +93,6 @@ struct SsspParams {
     // full-SSSP mode
     const int32_t* sources;  // [nslots]
     float* out_d32;          // [nslots][n]
-    int32_t* out_pred;       // nullable
     // voronoi mode
     int voronoi;
     int32_t center, code;
@@ -539,29 +538,6 @@ __global__ void __launch_bounds__(kThreads, GEOCB_SSSP_MINBLOCKS) sssp_kernel(Ss
     } else {
         for (int64_t i = gtid; i < (int64_t)B * n; i += gthreads)
             p.out_d32[i] = __double2float_rn(__longlong_as_double((long long)p.dist[i]));
-        if (p.out_pred) {
-            constexpr int kGroup = 8;  // lanes per vertex; shuffles name only the group's own lanes
-            const int lane = threadIdx.x & (kGroup - 1);
-            const unsigned gmask = ((1u << kGroup) - 1u) << (((threadIdx.x & 31) / kGroup) * kGroup);
-            const int64_t ggroup = gtid / kGroup, ngroupsp = gthreads / kGroup;
-            for (int64_t item = ggroup; item < (int64_t)B * n; item += ngroupsp) {
-                const int s = (int)(item / n);
-                const int64_t v = item - (int64_t)s * n;
-                const u64* dist_s = p.dist + (int64_t)s * n;
-                const u64 dv = dist_s[v];
-                int best = 0x7fffffff;
-                if (dv != D64_INF_BITS && v != p.sources[s]) {
-                    const int64_t beg = p.row_ptr[v], end = p.row_ptr[v + 1];
-                    for (int64_t i = beg + lane; i < end; i += kGroup) {
-                        const uint2 e = p.adj[i];
-                        const double c0 = __longlong_as_double((long long)dist_s[e.x]) + (double)__uint_as_float(e.y);
-                        if ((u64)__double_as_longlong(c0) == dv && (int)e.x < best) best = (int)e.x;
-                    }
-                }
-                for (int o = kGroup / 2; o; o >>= 1) best = min(best, __shfl_xor_sync(gmask, best, o, kGroup));
-                if (lane == 0) p.out_pred[item] = best == 0x7fffffff ? -9999 : best;
-            }
-        }
     }
     if (p.stats) {
         if (gtid == 0) {
@@ -580,6 +556,37 @@ __global__ void __launch_bounds__(kThreads, GEOCB_SSSP_MINBLOCKS) sssp_kernel(Ss
             atomicAdd(p.stats + 1, (u64)n_rounds);
             atomicAdd(p.stats + 2, (u64)n_scans);
         }
+    }
+}
+
+// Predecessors from the converged fp64 distances: pred[s][v] = lowest-index u with an edge u->v and
+// fl64(dist[u] + w(u,v)) == dist[v]  (-9999 for the source and unreachable vertices, scipy's convention).
+// The scan runs over v's IN-edges, so a directed graph passes the adjacency of its transpose (in_row_ptr / in_adj);
+// a symmetric graph passes its own.  8 lanes per vertex.
+__global__ void sssp_pred_kernel(const int64_t* in_row_ptr, const uint2* in_adj, int64_t n, int B, const u64* dist,
+                                 const int32_t* sources, int32_t* out_pred) {
+    constexpr int kGroup = 8;  // shuffles name only the group's own lanes
+    const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
+    const int lane = threadIdx.x & (kGroup - 1);
+    const unsigned gmask = ((1u << kGroup) - 1u) << (((threadIdx.x & 31) / kGroup) * kGroup);
+    const int64_t ggroup = gtid / kGroup, ngroupsp = gthreads / kGroup;
+    for (int64_t item = ggroup; item < (int64_t)B * n; item += ngroupsp) {
+        const int s = (int)(item / n);
+        const int64_t v = item - (int64_t)s * n;
+        const u64* dist_s = dist + (int64_t)s * n;
+        const u64 dv = dist_s[v];
+        int best = 0x7fffffff;
+        if (dv != D64_INF_BITS && v != sources[s]) {
+            const int64_t beg = in_row_ptr[v], end = in_row_ptr[v + 1];
+            for (int64_t i = beg + lane; i < end; i += kGroup) {
+                const uint2 e = in_adj[i];
+                const double c0 = __longlong_as_double((long long)dist_s[e.x]) + (double)__uint_as_float(e.y);
+                if ((u64)__double_as_longlong(c0) == dv && (int)e.x < best) best = (int)e.x;
+            }
+        }
+        for (int o = kGroup / 2; o; o >>= 1) best = min(best, __shfl_xor_sync(gmask, best, o, kGroup));
+        if (lane == 0) out_pred[item] = best == 0x7fffffff ? -9999 : best;
     }
 }
 
@@ -673,9 +680,12 @@ GEOCB_API int64_t geocb_voronoi_workspace_bytes(int64_t n) {
 
 GEOCB_API int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t n, const int32_t* sources, int S,
                                double delta, int slots, void* workspace, int64_t workspace_bytes, float* out_d32,
-                               int32_t* out_pred, int64_t* stats_host, void* stream) {
+                               int32_t* out_pred, const int64_t* in_row_ptr, const void* in_adj, int64_t* stats_host,
+                               void* stream) {
     ARG_CHECK(row_ptr && adj && sources && out_d32 && workspace);
+    ARG_CHECK((in_row_ptr == nullptr) == (in_adj == nullptr));
     ARG_CHECK(n > 0 && n < (1LL << 31) - 64 && S > 0 && slots >= 1 && slots <= kMaxSlots && delta > 0);
+    // (adjacency offsets are 32-bit inside the kernel: geocb_adj_count refuses graphs with >= 2^32 pairs)
     WsLayout w = ws_layout(n, slots, true);
     if (workspace_bytes < w.total) {
         geocb_set_error("sssp workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)w.total);
@@ -694,11 +704,16 @@ GEOCB_API int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t 
         p.stats = (u64*)(ws + w.stats);
         p.sources = sources + s0;
         p.out_d32 = out_d32 + (int64_t)s0 * n;
-        p.out_pred = out_pred ? out_pred + (int64_t)s0 * n : nullptr;
         p.voronoi = 0;
         if (s0 + slots < S || s0 > 0) CU_TRY(cudaMemsetAsync(ws + w.stats + 64, 0, kStatsBytes - 64, st));  // trace = last launch
         void* args[] = {&p};
         CU_TRY(cudaLaunchCooperativeKernel((void*)sssp_kernel, dim3(grid), dim3(kThreads), args, 0, st));
+        if (out_pred) {
+            sssp_pred_kernel<<<grid * 2, 256, 0, st>>>(in_row_ptr ? in_row_ptr : row_ptr,
+                                                       (const uint2*)(in_adj ? in_adj : adj), n, p.nslots, p.dist,
+                                                       p.sources, out_pred + (int64_t)s0 * n);
+            KERNEL_CHECK();
+        }
     }
     if (stats_host) CU_TRY(cudaMemcpyAsync(stats_host, ws + w.stats, 32, cudaMemcpyDeviceToHost, st));
     int failed = 0;
@@ -748,7 +763,7 @@ GEOCB_API int geocb_voronoi_insert(const int64_t* row_ptr, const void* adj, int6
     fill_params(p, w, ws, row_ptr, adj, n, delta);
     p.nslots = 1;
     p.dist = (u64*)dmin64;
-    p.stats = nullptr;
+    p.stats = nullptr;  // (p.failed still points into the stats block: read back by geocb_voronoi_check)
     p.voronoi = 1;
     p.center = center;
     p.code = code;
@@ -756,5 +771,19 @@ GEOCB_API int geocb_voronoi_insert(const int64_t* row_ptr, const void* adj, int6
     p.label = label;
     void* args[] = {&p};
     CU_TRY(cudaLaunchCooperativeKernel((void*)sssp_kernel, dim3(grid), dim3(kThreads), args, 0, (cudaStream_t)stream));
+    return 0;
+}
+
+GEOCB_API int geocb_voronoi_check(int64_t n, void* workspace, int64_t workspace_bytes, void* stream) {
+    ARG_CHECK(n > 0 && workspace);
+    WsLayout w = ws_layout(n, 1, false);
+    ARG_CHECK(workspace_bytes >= w.total);
+    int failed = 0;
+    CU_TRY(cudaMemcpyAsync(&failed, (char*)workspace + w.stats + 40, 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    CU_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+    if (failed) {
+        geocb_set_error("a voronoi insert hit the round limit without converging");
+        return GEOCB_ERR_OVERFLOW;
+    }
     return 0;
 }

@@ -80,11 +80,6 @@ __device__ __forceinline__ uint64_t policy_evict_first() {
 }
 __device__ __forceinline__ uint32_t ub_floor(double c) { return __float_as_uint(__double2float_rd(c)); }
 __device__ __forceinline__ uint32_t ub_ceil(double c) { return __float_as_uint(__double2float_ru(c)); }
-__device__ __forceinline__ uint32_t ld_ub(const uint32_t* p, uint64_t pol) {
-    uint32_t v;
-    asm volatile("ld.global.cg.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
-    return v;
-}
 __device__ __forceinline__ void red_min_ub(uint32_t* p, uint32_t val, uint64_t pol) {
     asm volatile("red.global.min.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(p), "r"(val), "l"(pol) : "memory");
 }
@@ -118,31 +113,35 @@ __device__ __forceinline__ u64 now_ns() {
     return t;
 }
 
-// The set bits of `any` are handed out two at a time: half-warp 0 takes the lowest, half-warp 1 the next one
-// (-1 when there is none).  Warp-uniform control, `any` is consumed.
-__device__ __forceinline__ int take_pair(unsigned& any, int half) {
-    const int j0 = __ffs(any) - 1;
-    any &= any - 1;
-    const int j1 = any ? __ffs(any) - 1 : -1;
-    any &= any - 1;  // (0 & anything == 0)
-    return half ? j1 : j0;
+#ifndef GEOCB_VM_MINBLOCKS
+#define GEOCB_VM_MINBLOCKS 3
+#endif
+constexpr int kDuStride = G + 2;  // u64 words per staged vertex row: 144 B keeps 16-byte alignment, spreads banks
+
+__device__ __forceinline__ uint4 ld_ub4(const uint32_t* p, uint64_t pol) {
+    uint4 v;
+    asm volatile("ld.global.cg.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(p), "l"(pol));
+    return v;
 }
 
-__global__ void __launch_bounds__(kThreads, 3) sssp_vm_kernel(VmParams p) {
+__global__ void __launch_bounds__(kThreads, GEOCB_VM_MINBLOCKS) sssp_vm_kernel(VmParams p) {
     cg::grid_group grid = cg::this_grid();
     const int64_t n = p.n;
     const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
     const int64_t gwarp = gtid >> 5, nwarps = gthreads >> 5;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int s = lane & 15, half = lane >> 4;
+    const int Q = lane >> 2, q = lane & 3;  // edge pass: quad Q of the warp = one edge, lane q of the quad = slots 4q..4q+3
     const int64_t nchunks = (n + 31) >> 5;
     const int B = p.B;
     VmCtl* ctl = p.ctl;
 
-    __shared__ u64 s_du[kWarps][32][G];   // popped vertices' own distances (fp64 bits), [vertex of the chunk][slot]
-    __shared__ uint4 s_rec[kWarps][32];   // one tile of edges: {target*G, owner vertex of the chunk, weight as fp64}
+    __shared__ __align__(16) u64 s_du[kWarps][32][kDuStride];  // popped vertices' own distances (fp64 bits), [vertex of the chunk][slot]
+    __shared__ uint4 s_rec[kWarps][2][32];  // two tiles of edges: {target*G, owner vertex of the chunk, weight as fp64}
     __shared__ double s_thr[G], s_hint[G];
+    __shared__ float s_thrn[G];
     __shared__ int s_epoch[G], s_done[G], s_need[G];
     __shared__ int s_flag, s_alldone;
     const uint64_t pol_keep = policy_evict_last();
@@ -174,23 +173,22 @@ __global__ void __launch_bounds__(kThreads, 3) sssp_vm_kernel(VmParams p) {
     }
     grid.sync();
     if (gtid < G) {
-        const int q = (int)gtid;
-        ctl->thr2[q][0] = ctl->thr2[q][1] = p.delta;
-        for (int i = 0; i < 3; ++i) ctl->scan_min[q][i] = F32_INF_BITS, ctl->scan_pushed[q][i] = 0, ctl->active[q][i] = 0;
-        if (q < 3) ctl->nact[q] = 0;
-        if (q < p.nslots) {
-            const int64_t src = p.sources[q];
-            p.dist[src * G + q] = 0ULL;
-            p.ub[src * G + q] = 0u;
-            atomicOr(p.mask[0] + src, 1u << q);
-            ctl->active[q][0] = 1;
+        const int g = (int)gtid;
+        ctl->thr2[g][0] = ctl->thr2[g][1] = p.delta;
+        for (int i = 0; i < 3; ++i) ctl->scan_min[g][i] = F32_INF_BITS, ctl->scan_pushed[g][i] = 0, ctl->active[g][i] = 0;
+        if (g < 3) ctl->nact[g] = 0;
+        if (g < p.nslots) {
+            const int64_t src = p.sources[g];
+            p.dist[src * G + g] = 0ULL;
+            p.ub[src * G + g] = 0u;
+            atomicOr(p.mask[0] + src, 1u << g);
+            ctl->active[g][0] = 1;
         }
     }
     grid.sync();
 
     unsigned n_improve = 0, n_rounds = 0, n_scans = 0, n_blocked = 0;
     u64 n_relax = 0, n_visit = 0;
-    const uint32_t* ubl = p.ub + s;
 
     for (int round = 0;; ++round) {
         const int c_cur = round % 3, c_next = (round + 1) % 3, c_clear = (round + 2) % 3;
@@ -200,39 +198,44 @@ __global__ void __launch_bounds__(kThreads, 3) sssp_vm_kernel(VmParams p) {
         if (gtid == 0) ctl->nact[c_clear] = 0;         // last read before the previous round's A1
         if (threadIdx.x < G) s_thr[threadIdx.x] = ld_cg_f64(&ctl->thr2[threadIdx.x][s_epoch[threadIdx.x] & 1]);
         __syncthreads();
-        const double thr = s_thr[s];
         if (p.stats && gtid == 0 && round < 120) p.stats[8 + 2 * round] = now_ns();
 
-        // ---- A0: pop.  A (vertex, slot) pair is active iff its frontier bit is set and its distance dropped since
-        //      the vertex was last relaxed for that slot (proc); act[v] is written for every vertex. ----
+        // ---- A0: pop (lane = vertex).  A (vertex, slot) pair is active iff its frontier bit is set and its distance
+        //      dropped since the vertex was last relaxed for that slot (proc); act[v] is written for every vertex. ----
         {
             unsigned popped = 0, nactv = 0;
+            uint32_t m_nx = 0;
+            if (gwarp * 32 + lane < n) m_nx = ld_cg_u32(cur + gwarp * 32 + lane);
             for (int64_t c = gwarp; c < nchunks; c += nwarps) {
                 const int64_t v = c * 32 + lane;
-                uint32_t m = 0;
-                if (v < n) m = ld_cg_u32(cur + v);
-                unsigned any = __ballot_sync(FULL, m != 0);
+                const uint32_t m = m_nx;
+                m_nx = 0;
+                if ((c + nwarps) * 32 + lane < n) m_nx = ld_cg_u32(cur + (c + nwarps) * 32 + lane);  // next chunk's masks in flight
                 uint32_t my_act = 0;
-                if (any) {
-                    if (m) {
-                        cur[v] = 0;                       // consumed
-                        red_and_u32(p.dirty + v, ~m);     // popped pairs are no longer "far"
-                    }
-                    while (any) {
-                        const int j = take_pair(any, half);
-                        const uint32_t mj = __shfl_sync(FULL, m, j < 0 ? 0 : j);
-                        bool a = false;
-                        if (j >= 0 && ((mj >> s) & 1u)) {
-                            const int64_t i = (c * 32 + j) * G + s;
-                            const u64 d = ld_cg_u64(p.dist + i), pr = ld_cg_u64(p.proc + i);
-                            a = d < pr;
-                            if (a) p.proc[i] = d;
+                if (m) {
+                    cur[v] = 0;                    // consumed
+                    red_and_u32(p.dirty + v, ~m);  // popped pairs are no longer "far"
+                    uint32_t mm = m;
+                    while (mm) {  // four (slot) pairs per trip, their loads independent
+                        int sk[4];
+                        u64 d[4], pr[4];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            sk[k] = mm ? __ffs(mm) - 1 : -1;
+                            mm &= mm - 1;  // (stays 0)
                         }
-                        const unsigned bal = __ballot_sync(FULL, a);
-                        const int j0 = __shfl_sync(FULL, j, 0), j1 = __shfl_sync(FULL, j, 16);
-                        if (lane == j0) my_act = bal & 0xffffu;
-                        if (lane == j1) my_act = bal >> 16;
-                        popped += __popc(bal);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            if (sk[k] >= 0) {
+                                d[k] = ld_cg_u64(p.dist + v * G + sk[k]);
+                                pr[k] = ld_cg_u64(p.proc + v * G + sk[k]);
+                            }
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            if (sk[k] >= 0 && d[k] < pr[k]) {
+                                p.proc[v * G + sk[k]] = d[k];
+                                my_act |= 1u << sk[k];
+                            }
                     }
                 }
                 if (v < n) p.act[v] = my_act;
@@ -240,11 +243,15 @@ __global__ void __launch_bounds__(kThreads, 3) sssp_vm_kernel(VmParams p) {
                     const uint32_t deg = __ldg(p.blk + (int64_t)B * n + v) - __ldg(p.blk + v);
                     n_relax += (u64)__popc(my_act) * deg;
                     n_visit += deg;
+                    popped += __popc(my_act);
                 }
                 nactv += __popc(__ballot_sync(FULL, my_act != 0));
             }
             if (lane == 0 && nactv) atomicAdd(&ctl->nact[c_cur], (u64)nactv);
-            if (p.stats && round < 120 && lane == 0 && popped) atomicAdd(p.stats + 9 + 2 * round, (u64)popped);  // (popped is warp-uniform)
+            if (p.stats && round < 120) {
+                popped = __reduce_add_sync(FULL, popped);
+                if (lane == 0 && popped) atomicAdd(p.stats + 9 + 2 * round, (u64)popped);
+            }
         }
         grid.sync();
 
@@ -254,7 +261,8 @@ __global__ void __launch_bounds__(kThreads, 3) sssp_vm_kernel(VmParams p) {
             const int Beff = (B > 1 && nact >= p.blk_min_active) ? B : 1;
             n_blocked += Beff > 1;
             const int64_t nitems = (int64_t)Beff * nchunks;
-            bool near_any = false;
+            const double thr0 = s_thr[4 * q], thr1 = s_thr[4 * q + 1], thr2 = s_thr[4 * q + 2], thr3 = s_thr[4 * q + 3];
+            unsigned near_acc = 0;
             uint32_t a_nx = 0, lo_nx = 0, hi_nx = 0;
             auto fetch = [&](int64_t g, uint32_t& a, uint32_t& lo, uint32_t& hi) {
                 a = lo = hi = 0;
@@ -274,9 +282,8 @@ __global__ void __launch_bounds__(kThreads, 3) sssp_vm_kernel(VmParams p) {
                 const uint32_t a = a_nx, lo = lo_nx, hi = hi_nx;
                 fetch(g + nwarps, a_nx, lo_nx, hi_nx);  // next item's mask / offsets are in flight during this one
                 const uint32_t len = a ? hi - lo : 0;
-                unsigned have = __ballot_sync(FULL, len != 0);
-                if (!have) continue;
-                const int64_t c = g % nchunks;
+                if (!__ballot_sync(FULL, len != 0)) continue;
+                const int64_t v = (g % nchunks) * 32 + lane;
                 uint32_t incl = len;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
@@ -286,22 +293,11 @@ __global__ void __launch_bounds__(kThreads, 3) sssp_vm_kernel(VmParams p) {
                 const uint32_t start = incl - len;
                 const uint32_t T = __shfl_sync(FULL, incl, 31);
                 const uint32_t rowoff = lo - start;  // adj index of flat position f inside this vertex's segment = rowoff + f
-                // own distances of the active vertices -> shared memory (inactive slots: +inf, never improves anything)
-                while (have) {
-                    const int j = take_pair(have, half);
-                    const uint32_t aj = __shfl_sync(FULL, a, j < 0 ? 0 : j);
-                    if (j >= 0) {
-                        u64 d = D64_INF_BITS;
-                        if ((aj >> s) & 1u) d = ld_cg_u64(p.dist + ((c * 32 + j) * G + s));
-                        s_du[warp][j][s] = d;
-                    }
-                }
-                __syncwarp();
-                for (uint32_t tile = 0; tile < T; tile += 32) {
-                    // lane -> flat edge tile+lane; its owner is the last vertex of the chunk whose start <= position
-                    // (an empty segment shares its start with its successor, so it is never selected while f < T)
+                // lane -> flat edge tile+lane; its owner is the last vertex of the chunk whose start <= position
+                // (an empty segment shares its start with its successor, so it is never selected while f < T)
+                auto load_edge_tile = [&](uint32_t tile, uint2& e, int& j) {
                     const uint32_t f = tile + lane;
-                    int j = 0;
+                    j = 0;
 #pragma unroll
                     for (int st = 16; st; st >>= 1) {
                         const int probe = min(j + st, 31);
@@ -309,52 +305,89 @@ __global__ void __launch_bounds__(kThreads, 3) sssp_vm_kernel(VmParams p) {
                         if (j + st <= 31 && t <= f) j += st;
                     }
                     const uint32_t off = __shfl_sync(FULL, rowoff, j);
-                    uint2 e = make_uint2(0u, F32_INF_BITS);
+                    e = make_uint2(0u, F32_INF_BITS);  // pad: vertex 0, +inf weight -> never improves anything
                     if (f < T) e = ld_edge(p.adj + (uint32_t)(off + f), pol_stream);
+                };
+                uint2 e_nx;
+                int j_nx;
+                load_edge_tile(0, e_nx, j_nx);  // in flight while the distances are staged
+                // own distances of the active (vertex, slot) pairs -> shared memory (lane = vertex); inactive: +inf
+#pragma unroll
+                for (int h = 0; h < G; h += 8) {
+                    u64 d[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        d[k] = D64_INF_BITS;
+                        if (len != 0 && ((a >> (h + k)) & 1u)) d[k] = ld_cg_u64(p.dist + v * G + h + k);
+                    }
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) s_du[warp][lane][h + k] = d[k];
+                }
+                auto publish = [&](int buf, uint2 e, int j) {
                     const double w = (double)__uint_as_float(e.y);
-                    s_rec[warp][lane] = make_uint4(e.x * G, (uint32_t)j, (uint32_t)__double2loint(w), (uint32_t)__double2hiint(w));
+                    s_rec[warp][buf][lane] = make_uint4(e.x * G, (uint32_t)j, (uint32_t)__double2loint(w), (uint32_t)__double2hiint(w));
+                };
+                auto consume = [&](const uint4 u4, const uint4 r) {
+                    const ulonglong2* dp = reinterpret_cast<const ulonglong2*>(&s_du[warp][r.y][4 * q]);
+                    const ulonglong2 d01 = dp[0], d23 = dp[1];
+                    const double w = __hiloint2double((int)r.w, (int)r.z);
+                    const double c0 = __longlong_as_double((long long)d01.x) + w, c1 = __longlong_as_double((long long)d01.y) + w;
+                    const double c2 = __longlong_as_double((long long)d23.x) + w, c3 = __longlong_as_double((long long)d23.y) + w;
+                    // cand >= ub[t][s] (>= dist[t][s])  <=>  round_down_f32(cand) >= ub: nothing to do
+                    const bool p0 = ub_floor(c0) < u4.x, p1 = ub_floor(c1) < u4.y, p2 = ub_floor(c2) < u4.z, p3 = ub_floor(c3) < u4.w;
+                    const unsigned pm = (unsigned)p0 | ((unsigned)p1 << 1) | ((unsigned)p2 << 2) | ((unsigned)p3 << 3);
+                    if (__any_sync(FULL, pm != 0)) {
+                        unsigned nm = 0;
+                        u64* dt = p.dist + r.x + 4 * q;
+                        uint32_t* ut = p.ub + r.x + 4 * q;
+                        if (p0) { red_min_u64(dt + 0, (u64)__double_as_longlong(c0)); red_min_ub(ut + 0, ub_ceil(c0), pol_keep); nm |= c0 < thr0 ? 1u : 0u; }
+                        if (p1) { red_min_u64(dt + 1, (u64)__double_as_longlong(c1)); red_min_ub(ut + 1, ub_ceil(c1), pol_keep); nm |= c1 < thr1 ? 2u : 0u; }
+                        if (p2) { red_min_u64(dt + 2, (u64)__double_as_longlong(c2)); red_min_ub(ut + 2, ub_ceil(c2), pol_keep); nm |= c2 < thr2 ? 4u : 0u; }
+                        if (p3) { red_min_u64(dt + 3, (u64)__double_as_longlong(c3)); red_min_ub(ut + 3, ub_ceil(c3), pol_keep); nm |= c3 < thr3 ? 8u : 0u; }
+                        near_acc |= nm;
+                        n_improve += __popc(pm);
+                        // near marks in bits 0..15, far marks in bits 16..31, combined over the quad
+                        unsigned packed = (nm | ((pm & ~nm) << 16)) << (4 * q);
+                        packed |= __shfl_xor_sync(FULL, packed, 1);
+                        packed |= __shfl_xor_sync(FULL, packed, 2);
+                        if (q == 0 && packed) {
+                            const uint32_t t = r.x / G;
+                            if (packed & 0xffffu) red_or_u32(next + t, packed & 0xffffu);
+                            if (packed >> 16) red_or_u32(p.dirty + t, packed >> 16);
+                        }
+                    }
+                };
+                publish(0, e_nx, j_nx);
+                __syncwarp();
+                uint4 u[4];
+                {
+                    const int ng0 = (int)min(4u, (T + 7) >> 3);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        if (i < ng0) u[i] = ld_ub4(p.ub + s_rec[warp][0][8 * i + Q].x + 4 * q, pol_keep);
+                }
+                if (32 < T) load_edge_tile(32, e_nx, j_nx);
+                int buf = 0;
+                for (uint32_t tile = 0; tile < T; tile += 32, buf ^= 1) {
+                    const bool more = tile + 32 < T;
+                    if (more) publish(buf ^ 1, e_nx, j_nx);  // records of the next tile
                     __syncwarp();
-                    const int nsteps = (int)min(16u, (T - tile + 1) >> 1);
-#pragma unroll 1
-                    for (int k0 = 0; k0 < nsteps; k0 += 8) {
-                        uint32_t uv[8];
+                    if (tile + 64 < T) load_edge_tile(tile + 64, e_nx, j_nx);  // edges two tiles ahead are in flight
+                    const int ng = (int)min(4u, (T - tile + 7) >> 3);
+                    const int ngn = more ? (int)min(4u, (T - tile - 32 + 7) >> 3) : 0;
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) {  // 8 gathers in flight (steps beyond the tile hit vertex 0 / +inf weight)
-                            const uint32_t toff = s_rec[warp][2 * (k0 + k) + half].x;
-                            uv[k] = ld_ub(ubl + toff, pol_keep);
-                        }
-#pragma unroll
-                        for (int k = 0; k < 8; ++k) {
-                            const uint4 r = s_rec[warp][2 * (k0 + k) + half];
-                            const double du = __longlong_as_double((long long)s_du[warp][r.y][s]);
-                            const double cand = du + __hiloint2double((int)r.w, (int)r.z);
-                            // cand >= ub[t][s] (>= dist[t][s])  <=>  round_down_f32(cand) >= ub: nothing to do
-                            const bool pass = ub_floor(cand) < uv[k];
-                            if (__ballot_sync(FULL, pass)) {
-                                bool nearb = false;
-                                if (pass) {
-                                    red_min_u64(p.dist + r.x + s, (u64)__double_as_longlong(cand));
-                                    red_min_ub(p.ub + r.x + s, ub_ceil(cand), pol_keep);
-                                    nearb = cand < thr;
-                                    near_any |= nearb;
-                                    ++n_improve;
-                                }
-                                const unsigned nb = __ballot_sync(FULL, pass && nearb);
-                                const unsigned fb = __ballot_sync(FULL, pass && !nearb);
-                                if (s == 0) {  // one lane per half-warp publishes the 16 slots' marks of this target
-                                    const uint32_t nbits = (nb >> (16 * half)) & 0xffffu, fbits = (fb >> (16 * half)) & 0xffffu;
-                                    const uint32_t t = r.x / G;
-                                    if (nbits) red_or_u32(next + t, nbits);
-                                    if (fbits) red_or_u32(p.dirty + t, fbits);
-                                }
-                            }
-                        }
+                    for (int i = 0; i < 4; ++i) {
+                        // consume group i of this tile, then reuse its registers for group i of the next tile:
+                        // three to four gather groups (24-32 edges x 16 slots) stay in flight per warp
+                        if (i < ng) consume(u[i], s_rec[warp][buf][8 * i + Q]);
+                        if (i < ngn) u[i] = ld_ub4(p.ub + s_rec[warp][buf ^ 1][8 * i + Q].x + 4 * q, pol_keep);
                     }
                     __syncwarp();
                 }
             }
-            // per-lane = per-slot: this warp set near-frontier bits for slot s
-            if (near_any) *(volatile int*)&ctl->active[s][c_next] = 1;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if ((near_acc >> k) & 1u) *(volatile int*)&ctl->active[4 * q + k][c_next] = 1;
         }
         grid.sync();
         ++n_rounds;
@@ -367,68 +400,75 @@ __global__ void __launch_bounds__(kThreads, 3) sssp_vm_kernel(VmParams p) {
         if (threadIdx.x == 0) s_flag = 0;
         __syncthreads();
         if (threadIdx.x < G) {
-            const int q = threadIdx.x;
-            const int need = !s_done[q] && ld_cg_s32(&ctl->active[q][c_next]) == 0;
-            s_need[q] = need;
+            const int g = threadIdx.x;
+            const int need = !s_done[g] && ld_cg_s32(&ctl->active[g][c_next]) == 0;
+            s_need[g] = need;
             if (need) s_flag = 1;
+            double thr_new = s_thr[g] + p.delta;
+            if (s_hint[g] > thr_new) thr_new = s_hint[g];
+            // ub (f32) < thr_new (fp64)  <=>  ub < round_up_f32(thr_new)
+            s_thrn[g] = __double2float_ru(thr_new);
+            if (need && blockIdx.x == 0) ctl->thr2[g][(s_epoch[g] + 1) & 1] = thr_new;
         }
         __syncthreads();
         if (s_flag) {
             ++n_scans;
-            // ---- phase B: raise the threshold of every dry slot, move its dirty vertices below it to the frontier ----
+            // ---- phase B (lane = vertex): raise the threshold of every dry slot, move its dirty vertices below it to
+            //      the frontier; remember the smallest bound left behind (to jump over empty buckets) ----
             uint32_t needmask = 0;
-            for (int q = 0; q < G; ++q) needmask |= s_need[q] ? (1u << q) : 0u;
-            double thr_new = s_thr[s] + p.delta;
-            if (s_hint[s] > thr_new) thr_new = s_hint[s];
-            uint32_t rem_min = F32_INF_BITS;
-            int pushed = 0;
+#pragma unroll
+            for (int g = 0; g < G; ++g) needmask |= s_need[g] ? (1u << g) : 0u;
+            uint32_t rem[G];
+#pragma unroll
+            for (int g = 0; g < G; ++g) rem[g] = F32_INF_BITS;
+            uint32_t pushed_mask = 0;
             for (int64_t c = gwarp; c < nchunks; c += nwarps) {
                 const int64_t v = c * 32 + lane;
                 uint32_t dfull = 0;
                 if (v < n) dfull = ld_cg_u32(p.dirty + v);
                 const uint32_t dm = dfull & needmask;
-                unsigned any = __ballot_sync(FULL, dm != 0);
-                uint32_t taken = 0;
-                while (any) {
-                    const int j = take_pair(any, half);
-                    const uint32_t dj = __shfl_sync(FULL, dm, j < 0 ? 0 : j);
-                    bool take = false;
-                    if (j >= 0 && ((dj >> s) & 1u)) {
-                        const uint32_t u = ld_cg_u32(p.ub + (c * 32 + j) * G + s);
-                        take = (double)__uint_as_float(u) < thr_new;
-                        if (!take) rem_min = min(rem_min, u);
-                        pushed += take;
+                if (dm) {
+                    const uint32_t* row = p.ub + v * G;
+                    uint32_t ur[G];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const uint4 x = ld_ub4(row + 4 * i, pol_keep);
+                        ur[4 * i] = x.x, ur[4 * i + 1] = x.y, ur[4 * i + 2] = x.z, ur[4 * i + 3] = x.w;
                     }
-                    const unsigned bal = __ballot_sync(FULL, take);
-                    const int j0 = __shfl_sync(FULL, j, 0), j1 = __shfl_sync(FULL, j, 16);
-                    if (lane == j0) taken = bal & 0xffffu;
-                    if (lane == j1) taken = bal >> 16;
-                }
-                if (taken) {
-                    p.dirty[v] = dfull & ~taken;  // nothing else touches dirty/next[v] during a scan
-                    red_or_u32(next + v, taken);
+                    uint32_t taken = 0;
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        if ((dm >> g) & 1u) {
+                            if (__uint_as_float(ur[g]) < s_thrn[g]) taken |= 1u << g;
+                            else rem[g] = min(rem[g], ur[g]);
+                        }
+                    }
+                    if (taken) {
+                        p.dirty[v] = dfull & ~taken;  // nothing else touches dirty[v] / next[v] during a scan
+                        red_or_u32(next + v, taken);
+                        pushed_mask |= taken;
+                    }
                 }
             }
-            // lanes s and s+16 both accumulate slot s
-            rem_min = min(rem_min, __shfl_xor_sync(FULL, rem_min, 16));
-            pushed += __shfl_xor_sync(FULL, pushed, 16);
-            if (half == 0 && s_need[s]) {
-                if (rem_min != F32_INF_BITS) atomicMin(&ctl->scan_min[s][c_cur], rem_min);
+            pushed_mask = __reduce_or_sync(FULL, pushed_mask);
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                const uint32_t r = __reduce_min_sync(FULL, rem[g]);
                 // (active[c_next] must not be touched here: slower blocks may still be reading it to decide whether
                 //  to enter this phase, and its grid.sync, at all)
-                if (pushed) atomicAdd(&ctl->scan_pushed[s][c_cur], pushed);
-                if (gwarp == 0) ctl->thr2[s][(s_epoch[s] + 1) & 1] = thr_new;
+                if (lane == 0 && r != F32_INF_BITS) atomicMin(&ctl->scan_min[g][c_cur], r);
             }
+            if (lane < G && ((pushed_mask >> lane) & 1u)) atomicOr(&ctl->scan_pushed[lane][c_cur], 1);
             grid.sync();
             if (threadIdx.x < G && s_need[threadIdx.x]) {  // identical in every block
-                const int q = threadIdx.x;
-                const int pu = ld_cg_s32(&ctl->scan_pushed[q][c_cur]);
-                const uint32_t mn = ld_cg_u32(&ctl->scan_min[q][c_cur]);
-                s_epoch[q] += 1;
-                s_hint[q] = 0.0;
+                const int g = threadIdx.x;
+                const int pu = ld_cg_s32(&ctl->scan_pushed[g][c_cur]);
+                const uint32_t mn = ld_cg_u32(&ctl->scan_min[g][c_cur]);
+                s_epoch[g] += 1;
+                s_hint[g] = 0.0;
                 if (pu == 0) {
-                    if (mn == F32_INF_BITS) s_done[q] = 1;  // frontier empty and nothing dirty: converged
-                    else s_hint[q] = (double)__uint_as_float(mn) + p.delta;  // jump over the gap
+                    if (mn == F32_INF_BITS) s_done[g] = 1;  // frontier empty and nothing dirty: converged
+                    else s_hint[g] = (double)__uint_as_float(mn) + p.delta;  // jump over the gap
                 }
             }
             __syncthreads();
@@ -447,7 +487,8 @@ __global__ void __launch_bounds__(kThreads, 3) sssp_vm_kernel(VmParams p) {
 
     // ---- finalize: out_d32[s][v] = f32(dist[v][s]), transposed through shared memory (coalesced both ways) ----
     {
-        float* tile = reinterpret_cast<float*>(&s_du[warp][0][0]);  // [G][33] floats = 2112 B of this warp's 4096
+        float* tile = reinterpret_cast<float*>(&s_du[warp][0][0]);  // [G][33] floats = 2112 B of this warp's 4608
+        const int s = lane & 15, half = lane >> 4;
         for (int64_t c = gwarp; c < nchunks; c += nwarps) {
 #pragma unroll 4
             for (int k = 0; k < 16; ++k) {
@@ -460,7 +501,7 @@ __global__ void __launch_bounds__(kThreads, 3) sssp_vm_kernel(VmParams p) {
             __syncwarp();
             const int64_t v = c * 32 + lane;
             if (v < n)
-                for (int q = 0; q < p.nslots; ++q) p.out_d32[(int64_t)q * n + v] = tile[q * 33 + lane];
+                for (int g = 0; g < p.nslots; ++g) p.out_d32[(int64_t)g * n + v] = tile[g * 33 + lane];
             __syncwarp();
         }
     }

@@ -19,6 +19,39 @@ def _i64():
     return C.c_int64(0)
 
 
+# ------------------------------------------------------------ host <-> device staging
+_STAGE_CHUNK = 32 << 20
+_stage_bufs = {}
+
+
+def h2d(arr: np.ndarray, dev) -> torch.Tensor:
+    """Pageable NumPy array -> device tensor through two pinned staging buffers: the (multi-threaded) host copy of
+    chunk i+1 into pinned memory overlaps the DMA of chunk i, so large arrays move at PCIe speed instead of the
+    driver's pageable-copy speed.  Small arrays take the plain path."""
+    arr = np.ascontiguousarray(arr)
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")  # read-only NumPy buffers (scipy views): we only read
+        src = torch.from_numpy(arr)
+    if src.numel() * src.element_size() < (8 << 20):
+        return src.to(dev)
+    out = torch.empty(src.shape, dtype=src.dtype, device=dev)
+    sb, db = src.view(torch.uint8).reshape(-1), out.view(torch.uint8).reshape(-1)
+    key = torch.device(dev).index
+    if key not in _stage_bufs:
+        _stage_bufs[key] = [torch.empty(_STAGE_CHUNK, dtype=torch.uint8).pin_memory() for _ in range(2)]
+    bufs, evs = _stage_bufs[key], [None, None]
+    for i, off in enumerate(range(0, sb.numel(), _STAGE_CHUNK)):
+        m = min(_STAGE_CHUNK, sb.numel() - off)
+        if evs[i & 1] is not None:
+            evs[i & 1].synchronize()  # the DMA out of this staging buffer has finished
+        bufs[i & 1][:m].copy_(sb[off:off + m])
+        db[off:off + m].copy_(bufs[i & 1][:m], non_blocking=True)
+        evs[i & 1] = torch.cuda.Event()
+        evs[i & 1].record()
+    return out
+
+
 class DeviceCSR:
     """CSR matrix in HBM: indptr int64[n+1], indices int32[nnz] (ascending per row), data f32[nnz]."""
 
@@ -35,9 +68,8 @@ class DeviceCSR:
         W = W.tocsr()
         if not W.has_sorted_indices:
             W = W.sorted_indices()
-        return cls(torch.from_numpy(W.indptr.astype(np.int64)).to(device),
-                   torch.from_numpy(W.indices.astype(np.int32)).to(device),
-                   torch.from_numpy(W.data.astype(np.float32)).to(device), W.shape[0])
+        return cls(h2d(W.indptr.astype(np.int64, copy=False), device), h2d(W.indices.astype(np.int32, copy=False), device),
+                   h2d(W.data.astype(np.float32, copy=False), device), W.shape[0])
 
     def to_scipy(self):
         from scipy import sparse
@@ -72,6 +104,31 @@ class DeviceCSR:
             check(lib.geocb_sssp_vm_blocks(ptr(row_ptr), ptr(adj), self.n, int(B), ptr(blk), stream_ptr()), "sssp_vm_blocks")
             self._adj[key] = blk
         return self._adj[key]
+
+
+def csr_sym_check(g: DeviceCSR):
+    """(flags, extra): flags 1 = negative weight, 2 = structurally asymmetric, 4 = weights differ across the diagonal."""
+    lib = _lib.load()
+    extra = torch.empty(g.n, dtype=torch.int32, device=g.indptr.device)
+    flags = C.c_int(0)
+    check(lib.geocb_csr_sym_check(ptr(g.indptr), ptr(g.indices), ptr(g.data), g.n, ptr(extra), C.byref(flags),
+                                  stream_ptr()), "csr_sym_check")
+    return flags.value, extra
+
+
+def csr_undirected(g: DeviceCSR, extra):
+    """scipy's directed=False view: edge {i,j} if either direction is stored, weight = the smaller stored value."""
+    lib = _lib.load()
+    dev = g.indptr.device
+    indptr = torch.empty(g.n + 1, dtype=torch.int64, device=dev)
+    nnz = _i64()
+    check(lib.geocb_csr_undirected_count(ptr(g.indptr), ptr(extra), g.n, ptr(indptr), C.byref(nnz), stream_ptr()),
+          "csr_undirected_count")
+    indices = torch.empty(nnz.value, dtype=torch.int32, device=dev)
+    data = torch.empty(nnz.value, dtype=torch.float32, device=dev)
+    check(lib.geocb_csr_undirected_fill(ptr(g.indptr), ptr(g.indices), ptr(g.data), g.n, ptr(indptr), ptr(indices),
+                                        ptr(data), stream_ptr()), "csr_undirected_fill")
+    return DeviceCSR(indptr, indices, data, g.n)
 
 
 # --------------------------------------------------------------------------- kNN
@@ -248,8 +305,9 @@ def sssp_multi_vm(g: DeviceCSR, sources, unweighted=False, delta=None, out=None,
 
 
 def sssp_multi(g: DeviceCSR, sources, unweighted=False, want_pred=False, delta=None, slots=None, out=None,
-               stats=False, kernel=None):
-    """S independent SSSPs -> D32[S,n] (+pred int32[S,n]) on the device."""
+               stats=False, kernel=None, g_in: DeviceCSR | None = None):
+    """S independent SSSPs -> D32[S,n] (+pred int32[S,n]) on the device.
+    g_in: transpose of a directed (asymmetric) g -- predecessors are searched over in-edges."""
     lib = _lib.load()
     dev = g.indptr.device
     row_ptr, adj, mean_w = g.adjacency(unweighted)
@@ -268,8 +326,11 @@ def sssp_multi(g: DeviceCSR, sources, unweighted=False, want_pred=False, delta=N
     D = out if out is not None else torch.empty((S, g.n), dtype=torch.float32, device=dev)
     P = torch.empty((S, g.n), dtype=torch.int32, device=dev) if want_pred else None
     st = (C.c_int64 * 4)()
+    in_ptr = in_adj = None
+    if want_pred and g_in is not None:
+        in_ptr, in_adj, _ = g_in.adjacency(unweighted)
     check(lib.geocb_sssp_multi(ptr(row_ptr), ptr(adj), g.n, ptr(src), S, float(delta), slots, ptr(ws), ws.numel(),
-                               ptr(D), ptr(P), st, stream_ptr()), "sssp_multi")
+                               ptr(D), ptr(P), ptr(in_ptr), ptr(in_adj), st, stream_ptr()), "sssp_multi")
     res = (D, P) if want_pred else D
     if stats:
         return res, dict(relaxations=st[0], rounds=st[1], scans=st[2], improvements=st[3], slots=slots, delta=delta,
@@ -278,7 +339,7 @@ def sssp_multi(g: DeviceCSR, sources, unweighted=False, want_pred=False, delta=N
 
 
 def sssp_multi_to_host(g: DeviceCSR, sources, out_host: torch.Tensor, unweighted=False, delta=None, slots=None,
-                       pred_host: torch.Tensor | None = None, kernel=None):
+                       pred_host: torch.Tensor | None = None, kernel=None, g_in: DeviceCSR | None = None):
     """S independent SSSPs whose (S,n) float32 result (and int32 predecessors) land in HOST tensors.
 
     The sources run in lock-step batches of `slots`; the device->host copy of batch i is issued on a side stream and
@@ -302,7 +363,7 @@ def sssp_multi_to_host(g: DeviceCSR, sources, out_host: torch.Tensor, unweighted
         if free[bi & 1] is not None:
             main.wait_event(free[bi & 1])
         res = sssp_multi(g, src[b0:b1], unweighted=unweighted, want_pred=pred_host is not None, delta=delta,
-                         slots=slots, out=buf, kernel=kernel)
+                         slots=slots, out=buf, kernel=kernel, g_in=g_in)
         side.wait_stream(main)
         with torch.cuda.stream(side):
             out_host[b0:b1].copy_(buf, non_blocking=True)
@@ -357,6 +418,10 @@ class VoronoiState:
         self.is_center[int(center)] = 1
         self.count += 1
 
+    def check(self):
+        """Inserts are asynchronous: surface a non-converged one (round limit) before its result is used."""
+        check(_lib.load().geocb_voronoi_check(self.g.n, ptr(self.ws), self.ws.numel(), stream_ptr()), "voronoi_insert")
+
     def draw(self, u):
         """One k-means++ draw with the host's MT19937 double u -> (index or -1, used_exact_path, probs_sum)."""
         lib = _lib.load()
@@ -368,6 +433,7 @@ class VoronoiState:
             check(lib.geocb_pairwise_plan_host(n, host), "pairwise_plan_host")
             self.plan = torch.from_numpy(np.frombuffer(host, dtype=np.int64).copy()).to(dev)
             self.kpp_ws = torch.empty(lib.geocb_kpp_workspace_bytes(n), dtype=torch.uint8, device=dev)
+        self.check()
         res = (C.c_int64 * 4)()
         check(lib.geocb_kpp_draw(ptr(self.dmin32), ptr(self.is_center), n, float(u), ptr(self.plan), ptr(self.kpp_ws),
                                  self.kpp_ws.numel(), res, stream_ptr()), "kpp_draw")

@@ -28,26 +28,28 @@ def ensure_valid_graph(W: sparse.spmatrix) -> sparse.spmatrix:
     return W.tocsr()
 
 
-def _undirected(W: sparse.csr_matrix) -> sparse.csr_matrix:
-    """scipy's directed=False semantics: an edge exists if either direction is stored and its
-    weight is the smaller of the two stored values."""
-    Wt = W.T.tocsr()
-    if (W != Wt).nnz == 0:
-        return W
-    both = W.sign().multiply(Wt.sign())
-    hi = W.maximum(Wt)
-    return (hi - hi.multiply(both) + W.minimum(Wt)).tocsr()
-
-
 def graph_to_device(W, directed: bool = False) -> dg.DeviceCSR:
-    """Validate + upload (or pass through an already device-resident graph)."""
+    """Validate + upload (or pass through an already device-resident graph).
+
+    Same checks and exception types as `ensure_valid_graph` (:13-21); the value checks run on the device next to
+    the symmetry test (`geocb_csr_sym_check`) instead of as host passes over the arrays, and scipy's
+    `directed=False` view (edge if either direction is stored, smaller weight wins) is merged on the device."""
     if isinstance(W, dg.DeviceCSR):
         return W
-    W = ensure_valid_graph(W)
+    if not sparse.isspmatrix(W):
+        raise TypeError("W must be a scipy sparse matrix")
+    if W.shape[0] != W.shape[1]:
+        raise ValueError("W must be square")
     dev = _lib.require_cuda()
-    if not directed:
-        W = _undirected(W)
-    return dg.DeviceCSR.from_scipy(W, dev)
+    g = dg.DeviceCSR.from_scipy(W, dev)
+    if g.n == 0 or g.nnz == 0:
+        return g
+    flags, extra = dg.csr_sym_check(g)
+    if flags & 1:
+        raise ValueError("Negative weights")
+    if not directed and (flags & 6):
+        g = dg.csr_undirected(g, extra)
+    return g
 
 
 def dijkstra_multi_source(W: sparse.spmatrix, sources, directed: bool = False, unweighted: bool = False,
@@ -59,6 +61,7 @@ def dijkstra_multi_source(W: sparse.spmatrix, sources, directed: bool = False, u
     src = np.asarray(sources, dtype=int)
     if g.n == 0:
         raise ValueError("empty graph")
+    src = np.where(src < 0, src + g.n, src)  # scipy wraps negative indices once (csgraph.dijkstra)
     if (src < 0).any() or (src >= g.n).any():
         raise ValueError("source index out of range")
     use_unit = bool(unweighted) and g.nnz > 0  # :31-33
@@ -68,10 +71,15 @@ def dijkstra_multi_source(W: sparse.spmatrix, sources, directed: bool = False, u
         if return_predecessors:
             return D, np.full((len(src), g.n), -9999, dtype=np.int32)
         return D
-    # device->host copies of one batch of sources overlap the next batch's kernel (dg.sssp_multi_to_host)
-    D = torch.empty((len(src), g.n), dtype=torch.float32)
-    P = torch.empty((len(src), g.n), dtype=torch.int32) if return_predecessors else None
-    dg.sssp_multi_to_host(g, src, D, unweighted=use_unit, pred_host=P)
+    # device->host copies of one batch of sources overlap the next batch's kernel (dg.sssp_multi_to_host); the result
+    # lands in pinned memory (torch's caching host allocator recycles the block once the caller drops the array)
+    big = len(src) * g.n * 4 >= (8 << 20)
+    D = torch.empty((len(src), g.n), dtype=torch.float32, pin_memory=big)
+    P = torch.empty((len(src), g.n), dtype=torch.int32, pin_memory=big) if return_predecessors else None
+    g_in = None
+    if return_predecessors and directed and not isinstance(W, dg.DeviceCSR):
+        g_in = dg.DeviceCSR.from_scipy(W.T.tocsr(), g.indptr.device)  # predecessors are searched over in-edges
+    dg.sssp_multi_to_host(g, src, D, unweighted=use_unit, pred_host=P, g_in=g_in)
     if return_predecessors:
         return D.numpy().astype(dtype, copy=False), P.numpy()  # :42
     return D.numpy().astype(dtype, copy=False)  # :50

@@ -69,6 +69,7 @@ def _labels_for(g, medoids):
 
 
 def _finish_assign(state, K):
+    state.check()  # a non-converged insert (round limit) must not pass silently
     assign = state.label.cpu().numpy().astype(int)
     assign[assign < 0] = 0  # argmin of an all-inf column is 0 (:100)
     counts = np.bincount(assign, minlength=K)

@@ -102,9 +102,9 @@ def build_knn_graph_faiss(z: np.ndarray, k: int = 10, metric: str = "euclidean",
 def build_knn_graph_auto(z: np.ndarray, k: int = 10, metric: str = "euclidean", mode: str = "distance",
                          sym: str = "mutual", force_method: Optional[str] = None,
                          size_threshold: int = 50000) -> Tuple[sparse.csr_matrix, Dict[str, np.ndarray]]:
-    """:129-170.  `force_method` / `size_threshold` are accepted for compatibility; the method is always cuda."""
-    if force_method not in (None, "sklearn", "faiss", "cuda"):
-        raise ValueError(f"Unknown force_method: {force_method}")
+    """:129-170.  `force_method` / `size_threshold` are accepted for compatibility; every value (including the
+    reference's "sklearn" / "faiss", and unknown strings, which the reference lets fall through to auto) resolves to
+    the one exact CUDA path, so `force_method="faiss"` works without faiss instead of raising (:153-156)."""
     print(f"Building k-NN graph: N={z.shape[0]}, k={k}, method=cuda")  # :164
     return _build(z, k, metric, mode, sym)
 
@@ -114,30 +114,30 @@ def largest_connected_component(W: sparse.csr_matrix) -> np.ndarray:
     n = W.shape[0]
     if n == 0:
         return np.ones(0, dtype=bool)
-    dev = _lib.require_cuda()
-    g = W if isinstance(W, dg.DeviceCSR) else dg.DeviceCSR.from_scipy(_undirected_structure(W), dev)
+    g = W if isinstance(W, dg.DeviceCSR) else _undirected_structure(W)
     mask, _, _, ncomp = dg.largest_component(g)
     if ncomp <= 1:
         return np.ones(n, dtype=bool)
     return mask.cpu().numpy().astype(bool)
 
 
-def _undirected_structure(W):
-    """connected_components(directed=False) sees an edge if either direction is stored."""
-    W = W.tocsr()
-    if (W != W.T).nnz == 0:
-        return W
-    S = W.copy()
-    S.data = np.ones_like(S.data)
-    return (S + S.T).tocsr()
+def _undirected_structure(W) -> dg.DeviceCSR:
+    """connected_components(directed=False) sees an edge if either direction is stored: upload, then merge the
+    missing directions on the device (geocb_csr_sym_check / geocb_csr_undirected_*)."""
+    dev = _lib.require_cuda()
+    g = dg.DeviceCSR.from_scipy(W, dev)
+    if g.nnz == 0:
+        return g
+    flags, extra = dg.csr_sym_check(g)
+    return dg.csr_undirected(g, extra) if flags & 2 else g
 
 
 def analyze_graph_connectivity(W: sparse.csr_matrix) -> Dict:
     """Connectivity statistics + the reference's printed lines (:184-219)."""
     N = W.shape[0]
     dev = _lib.require_cuda()
-    g = dg.DeviceCSR.from_scipy(_undirected_structure(W), dev)
-    labels = dg.component_labels(g)
+    g = _undirected_structure(W)
+    labels = dg.component_labels(g) if g.nnz else torch.arange(N, dtype=torch.int32, device=dev)
     sizes = torch.bincount(labels.long(), minlength=N)
     sizes = sizes[sizes > 0]
     n_components = int(sizes.numel())
