@@ -77,6 +77,19 @@ class DeviceCSR:
         ip = ip.astype(np.int32) if self.nnz < 2**31 - 1 else ip
         return sparse.csr_matrix((self.data.cpu().numpy(), self.indices.cpu().numpy(), ip), shape=(self.n, self.n))
 
+    def eliminate_zeros(self):
+        """Drop stored entries whose value is exactly 0 (what scipy's `A + A.T` does to the reference's W_geo,
+        build_codebook.py:53-54: an edge of Riemannian length 0 -- duplicate latents -- vanishes from the graph).
+        Returns self when nothing is stored as zero (the common case: one pass over the data)."""
+        keep = self.data != 0
+        if bool(keep.all()):
+            return self
+        rows = torch.repeat_interleave(torch.arange(self.n, device=self.data.device), self.indptr[1:] - self.indptr[:-1])
+        counts = torch.zeros(self.n, dtype=torch.int64, device=self.data.device).index_add_(0, rows[keep], torch.ones_like(rows[keep]))
+        indptr = torch.zeros(self.n + 1, dtype=torch.int64, device=self.data.device)
+        indptr[1:] = torch.cumsum(counts, 0)
+        return DeviceCSR(indptr, self.indices[keep].contiguous(), self.data[keep].contiguous(), self.n)
+
     # -- adjacency-pair form used by the SSSP kernels (rows padded to even length, 16 B aligned) --
     def adjacency(self, unit_weights=False):
         key = bool(unit_weights)
@@ -264,18 +277,15 @@ def vm_default_blocks(n):
 
 def _pick_kernel(kernel, S, want_pred):
     """'slot' = csrc/sssp.cu (one table per source), 'vm' = csrc/sssp_vm.cu (16 sources side by side per vertex).
-    'auto': vm for batches of sources wide enough to share edge loads and gathers; predecessors need 'slot'."""
+    'auto' = 'slot': on the C2 graph the vertex-major kernel shares an edge visit among only 3.8 of its 16 sources
+    and measures 66 G edge-relax/s against 125 G/s (profiles/r2_sssp_vm_*.txt); it stays selectable for graphs whose
+    sources overlap more.  Predecessors need 'slot'."""
     kernel = kernel or os.environ.get("GEOCB_SSSP_KERNEL", "auto")
     if kernel not in ("auto", "slot", "vm"):
         raise ValueError(f"unknown SSSP kernel '{kernel}'")
     if want_pred:
         return "slot"
-    if kernel == "auto":
-        return "vm" if S >= VM_MIN_SOURCES else "slot"
-    return kernel
-
-
-VM_MIN_SOURCES = int(os.environ.get("GEOCB_SSSP_VM_MIN_SOURCES", "8"))
+    return "slot" if kernel == "auto" else kernel
 
 
 def sssp_multi_vm(g: DeviceCSR, sources, unweighted=False, delta=None, out=None, stats=False, blocks=None,

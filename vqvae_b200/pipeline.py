@@ -137,6 +137,7 @@ def build_codebook_device(z4: torch.Tensor, decoder, k=20, sym="union", K=512, i
         g_geo.data[pos_ji] = L
     # ---- largest connected component (:56-63) ----
     tm("lcc")
+    g_geo = g_geo.eliminate_zeros()  # `W_geo + W_geo.T` (:54) drops zero-length edges (duplicate latents)
     mask, new_id, n_keep, _ = dg.largest_component(g_geo)
     if n_keep < M:
         if verbose and rank == 0:
