@@ -12,6 +12,13 @@ FASHION_CFG = dict(in_channels=1, output_image_size=28, latent_dim=16, enc_chann
                    dec_channels=[256, 128, 64], recon_loss="mse", norm_type="batch", mse_use_sigmoid=True)
 
 
+CIFAR_CFG = dict(in_channels=3, output_image_size=32, latent_dim=32, enc_channels=[64, 128, 256],
+                 dec_channels=[256, 128, 64], recon_loss="mse", norm_type="batch", mse_use_sigmoid=False)
+for p in (ROOT / "tools",):
+    if str(p) not in sys.path:
+        sys.path.insert(0, str(p))
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 
@@ -31,6 +38,25 @@ def s1(golden_dir):
 def c1(golden_dir):
     import numpy as np
     return dict(np.load(golden_dir / "c1_digest.npz"))
+
+
+@pytest.fixture(scope="session")
+def c3(golden_dir):
+    import numpy as np
+    return dict(np.load(golden_dir / "c3_digest.npz"))
+
+
+def c3_latents():
+    import torch
+    z4 = torch.randn(1250, 32, 4, 4, generator=torch.Generator().manual_seed(42))
+    return z4, z4.permute(0, 2, 3, 1).reshape(-1, 32).numpy()
+
+
+def cifar_decoder():
+    import torch
+    from vqvae_b200.models import SpatialVAE
+    torch.manual_seed(0)
+    return SpatialVAE(**CIFAR_CFG).decoder  # train mode, like the reference CLI
 
 
 def s1_latents():

@@ -215,8 +215,33 @@ def test_sssp_c1_graph_vs_oracle(geo, c1, slots):
             assert np.array_equal(D64[r][P2[r][v]] + w, D64[r][v])
 
 
-def test_sssp_c1_golden_digest(geo, c1, s1):
-    pass  # the c1 geodesic graph itself is not stored (size); covered through test_pipeline_c1
+def test_sssp_public_api_asymmetric_and_directed(geo):
+    """dijkstra_multi_source on host scipy matrices whose two directions differ (structure and weights): the
+    undirected view is merged on the device (geocb_csr_sym_check / geocb_csr_undirected_*) and must equal scipy's
+    directed=False result; directed=True with predecessors searches in-edges (transposed adjacency)."""
+    rs = np.random.RandomState(11)
+    n = 400
+    A = sparse.random(n, n, density=0.03, random_state=rs, format="csr", dtype=np.float32)
+    A.data = (A.data * 3 + 0.1).astype(np.float32)
+    A.setdiag(0)
+    A.eliminate_zeros()
+    src = [0, 5, 77, 399, -1]  # negative indices wrap like scipy's
+    for directed in (False, True):
+        D = geo["sp"].dijkstra_multi_source(A, src, directed=directed)
+        assert np.array_equal(D, oracle.sssp_multi(A, src, directed=directed)), directed
+        D2, P = geo["sp"].dijkstra_multi_source(A, src[:3], directed=directed, return_predecessors=True)
+        D64 = sparse.csgraph.dijkstra(A, directed=directed, indices=src[:3])
+        Ad = A.toarray().astype(np.float64)
+        Wd = Ad if directed else np.where((Ad > 0) & (Ad.T > 0), np.minimum(Ad, Ad.T), np.maximum(Ad, Ad.T))
+        for r in range(3):
+            v = np.nonzero(P[r] >= 0)[0]
+            assert len(v) == np.isfinite(D64[r]).sum() - 1
+            assert (Wd[P[r][v], v] > 0).all()
+            assert np.array_equal(D64[r][P[r][v]] + Wd[P[r][v], v], D64[r][v])
+    # components / LCC see an edge if either direction is stored
+    assert np.array_equal(geo["knn"].largest_connected_component(A), oracle.largest_component_mask(A))
+    with pytest.raises(ValueError):
+        geo["sp"].dijkstra_multi_source(A, [n])
 
 
 # ------------------------------------------------------------------ K-medoids

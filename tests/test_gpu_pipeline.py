@@ -22,24 +22,26 @@ def rel_err(a, b):
     return np.abs(a - b) / np.maximum(np.abs(b), 1e-30)
 
 
-def check_edge_lengths(got, ref):
-    """Tolerance 1e-5 relative (north star), with the ReLU-kink carve-out measured on the reference itself:
-    a pre-activation within float noise of 0 flips a ReLU mask and the JVP jumps.  The reference's own fp32
-    result differs from its fp64 evaluation by >1e-5 on 9 of 15641 s1 edges (0.06 %, max 3.5 %; script in
-    DESIGN.md), so: median <= 1e-6, at most 0.5 % of edges beyond 1e-5, none beyond 10 %."""
-    r = rel_err(got, ref)
-    assert np.median(r) <= 1e-6
-    assert (r > 1e-5).mean() < 5e-3, f"{(r > 1e-5).sum()} of {len(r)} edges off by >1e-5 (max {r.max():.3g})"
-    assert r.max() < 0.1
+def check_edge_lengths(got, ref, decoder, z_start, z_end, positions=None, batch_size=512):
+    """Tolerance 1e-5 relative on EVERY edge (north star), except edges that sit on a ReLU kink: an edge may exceed
+    1e-5 only if a float64 evaluation of the same decoder shows one of its pre-activations within EPS of 0 (its ReLU
+    mask is undecidable in float32), or -- through the BatchNorm batch means -- such a unit elsewhere in its 512-edge
+    batch and then by at most COUPLED_TOL.  Rule, constants and the measurement on the reference itself:
+    tools/kink_margin.py, profiles/r2_kink_margins.txt."""
+    import kink_margin
+    rep = kink_margin.check_edge_lengths(got, ref, decoder, z_start, z_end, batch_size, positions)
+    print("edge-length parity:", rep)
+    return rep
 
 
 def test_edge_lengths_s1_golden(s1):
     from vqvae_b200.geo.riemannian_metric import edge_lengths_riemannian
     _, zf = s1_latents()
     dec = fashion_decoder().cuda()
-    L = edge_lengths_riemannian(dec, torch.from_numpy(zf[s1["ei"]]), torch.from_numpy(zf[s1["ej"]]), batch_size=512)
+    a, b = torch.from_numpy(zf[s1["ei"]]), torch.from_numpy(zf[s1["ej"]])
+    L = edge_lengths_riemannian(dec, a, b, batch_size=512)
     assert L.dtype == torch.float32 and L.is_cuda and L.shape == (len(s1["ei"]),)
-    check_edge_lengths(L.cpu().numpy(), s1["edge_len"])
+    check_edge_lengths(L.cpu().numpy(), s1["edge_len"], fashion_decoder(), a, b)
 
 
 def test_edge_lengths_c1_sample(c1):
@@ -52,8 +54,69 @@ def test_edge_lengths_c1_sample(c1):
     ei, ej, pij, pji = dg.upper_edges(g)
     assert ei.numel() == int(c1["E"])
     L = edge_lengths_device(fashion_decoder().cuda(), z, ei, ej, 512).cpu().numpy()
-    check_edge_lengths(L[c1["edge_sample_pos"]], c1["edge_sample_len"])
+    zs, ze = torch.from_numpy(zf[ei.cpu().numpy()]), torch.from_numpy(zf[ej.cpu().numpy()])
+    check_edge_lengths(L[c1["edge_sample_pos"]], c1["edge_sample_len"], fashion_decoder(), zs, ze, c1["edge_sample_pos"])
     np.testing.assert_allclose([L.min(), L.mean(), L.max()], c1["edge_len_min_mean_max"], rtol=1e-4)
+
+
+def test_c3_cifar_shape_stages(c3):
+    """CIFAR-shape case (BASELINE configs[2] at 20k latents): d=32 kNN, 32-px decoder with BatchNorm (JVP output
+    P = 3x8x8 = 192), K=512 -- against the golden digests of the unmodified reference (make_golden.py --c3)."""
+    from vqvae_b200.pipeline import build_codebook_device
+    from vqvae_b200.geo import geo_shortest_paths as sp
+    from conftest import c3_latents, cifar_decoder
+    z4, zf = c3_latents()
+    assert sha(zf) == str(c3["z_sha"])
+    res = build_codebook_device(z4, cifar_decoder().cuda(), k=20, sym="union", K=512, verbose=False)
+    We = res.g_euc.to_scipy()
+    assert sha(We.indptr.astype(np.int32)) == str(c3["euc_indptr_sha"])
+    assert sha(We.indices.astype(np.int32)) == str(c3["euc_indices_sha"])
+    assert res.ei.numel() == int(c3["E"]) and res.g_lcc.nnz == int(c3["nnz"]) and res.g_lcc.n == int(c3["lcc_size"])
+    L = res.edge_len.cpu().numpy()
+    ei, ej = res.ei.cpu().numpy(), res.ej.cpu().numpy()
+    check_edge_lengths(L[c3["edge_sample_pos"]], c3["edge_sample_len"], cifar_decoder(), torch.from_numpy(zf[ei]),
+                       torch.from_numpy(zf[ej]), c3["edge_sample_pos"])
+    np.testing.assert_allclose([L.min(), L.mean(), L.max()], c3["edge_len_min_mean_max"], rtol=1e-4)
+    # geodesic distances on OUR graph vs the reference's on ITS graph (weights agree to ~1e-6): <= 1e-5 relative
+    D = sp.dijkstra_multi_source(res.g_lcc, c3["sssp_src"])[:, ::97]
+    r = rel_err(D, c3["sssp_D_sample"])
+    assert (r > 1e-5).mean() < 2e-3 and r.max() < 1e-3, (r.max(), (r > 1e-5).sum())
+    assert np.array_equal(res.medoids, c3["medoids"]), "c3 end-to-end medoids differ from the reference's"
+    assert sha(res.codes.astype(np.int32)) == str(c3["codes_sha"])
+    assert abs(res.qe - float(c3["qe"])) <= 1e-5 * float(c3["qe"])
+
+
+def test_sssp_c1_geodesic_sample(c1):
+    """Geodesic distances of the c1 pipeline graph against the reference's stored sample (c1_digest.npz sssp_D_sample;
+    the two graphs' weights agree to ~1e-6, ReLU-kink edges excepted): <= 1e-5 relative (north star)."""
+    from vqvae_b200.pipeline import build_codebook_device
+    from vqvae_b200.geo import geo_shortest_paths as sp
+    z4, _ = c1_latents()
+    res = build_codebook_device(z4, fashion_decoder().cuda(), k=20, sym="union", K=8, verbose=False)
+    D = sp.dijkstra_multi_source(res.g_lcc, c1["sssp_src"])[:, ::97]
+    r = rel_err(D, c1["sssp_D_sample"])
+    assert (r > 1e-5).mean() < 2e-3 and r.max() < 1e-3, (r.max(), (r > 1e-5).sum())
+
+
+def test_pipeline_duplicate_latents_vs_oracle():
+    """Duplicate latents give Riemannian length 0; the reference's `W_geo + W_geo.T` (build_codebook.py:53-54) drops
+    such entries, so duplicates can fall out of the LCC (code -1).  Structure, mask and codes must follow."""
+    import geo_oracle as oracle
+    from vqvae_b200.pipeline import build_codebook_device
+    z4 = torch.randn(60, 16, 4, 4, generator=torch.Generator().manual_seed(7))
+    zf = z4.permute(0, 2, 3, 1).reshape(-1, 16)
+    zf[10] = zf[3]
+    zf[200] = zf[3]
+    zf[511] = zf[510]
+    z4 = zf.reshape(60, 4, 4, 16).permute(0, 3, 1, 2).contiguous()
+    ref = oracle.build_codebook_arrays(z4, fashion_decoder(), k=10, sym="union", K=8, seed=3)
+    res = build_codebook_device(z4, fashion_decoder().cuda(), k=10, sym="union", K=8, seed=3, verbose=False)
+    Wg, Wr = res.g_geo.to_scipy(), ref["W_geo"].tocsr()
+    Wr.sort_indices()
+    assert Wg.nnz == Wr.nnz and np.array_equal(Wg.indptr, Wr.indptr) and np.array_equal(Wg.indices, Wr.indices)
+    assert (Wg.data != 0).all()
+    assert np.array_equal(res.mask.cpu().numpy().astype(bool), ref["mask"])
+    assert np.array_equal(res.medoids, ref["medoids"]) and np.array_equal(res.codes, ref["codes"])
 
 
 def test_edge_lengths_generic_decoder_properties():
@@ -87,7 +150,7 @@ def test_edge_lengths_other_norms_vs_oracle(norm):
     b = a + b
     L = edge_lengths_riemannian(dec.cuda(), a, b, batch_size=512).cpu()
     Lo = oracle.edge_lengths(dec.cpu(), a, b, 512)
-    check_edge_lengths(L.numpy(), Lo.numpy())
+    check_edge_lengths(L.numpy(), Lo.numpy(), dec.cpu(), a, b)
 
 
 def test_pipeline_s1_matches_golden(s1):
@@ -96,7 +159,9 @@ def test_pipeline_s1_matches_golden(s1):
     z4, _ = s1_latents()
     res = build_codebook_device(z4, fashion_decoder().cuda(), k=10, sym="union", K=32, verbose=False)
     assert np.array_equal(res.ei.cpu().numpy(), s1["ei"]) and np.array_equal(res.ej.cpu().numpy(), s1["ej"])
-    check_edge_lengths(res.edge_len.cpu().numpy(), s1["edge_len"])
+    _, zf = s1_latents()
+    check_edge_lengths(res.edge_len.cpu().numpy(), s1["edge_len"], fashion_decoder(), torch.from_numpy(zf[s1["ei"]]),
+                       torch.from_numpy(zf[s1["ej"]]))
     W = res.g_lcc.to_scipy()
     assert np.array_equal(W.indptr, s1["geo_indptr"]) and np.array_equal(W.indices, s1["geo_indices"])
     assert (W != W.T).nnz == 0
@@ -146,8 +211,7 @@ def test_cli_artifacts_c1(tmp_path, c1):
     assert torch.equal(cb["z_medoid"], torch.from_numpy(zf[cb["medoid_indices"]]))
     r = rel_err(W.data.min(), c1["edge_len_min_mean_max"][0])
     assert r < 1e-4
-    same_medoids = np.array_equal(cb["medoid_indices"], c1["medoids"].astype(np.int32))
-    print("c1 end-to-end medoids identical to the reference:", same_medoids)
-    if same_medoids:
-        assert sha(codes) == str(c1["codes_sha"])
+    # end to end the 512 medoids and all 20 000 codes equal the unmodified reference's (c1_digest.npz)
+    assert np.array_equal(cb["medoid_indices"], c1["medoids"].astype(np.int32)), "c1 end-to-end medoids differ"
+    assert sha(codes) == str(c1["codes_sha"])
     assert len(np.unique(codes)) == 512

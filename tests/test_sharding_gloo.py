@@ -9,7 +9,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from vqvae_b200.pipeline import all_gather_rows, shard_range
+from vqvae_b200.sharding import all_gather_rows, shard_range, allreduce_min_assignment
 
 
 def _free_port():
@@ -52,6 +52,21 @@ def _worker(rank, world, port, total, mult, q):
         best = key.min(dim=0).values
         dist.all_reduce(best, op=dist.ReduceOp.MIN)
         ok = ok and np.array_equal((best & 0xFFFFFFFF).numpy(), D.argmin(axis=0))
+        # the product helper (vqvae_b200.sharding.allreduce_min_assignment, used by kmeans_optimized._labels_for):
+        # per-rank Voronoi partials incl. unreachable vertices (+inf, -1), a vertex only one rank reaches, f32 ties
+        D2 = rng.rand(8, 60).astype(np.float32)
+        D2[:, 3] = np.inf          # nobody reaches vertex 3
+        D2[:4, 9] = np.inf         # only the second shard reaches vertex 9
+        D2[:, 11] = 0.25           # all tie -> k = 0
+        D2[2, 12] = D2[6, 12] = 0.0  # cross-rank tie -> k = 2
+        part = D2[klo:khi]
+        dmin = torch.from_numpy(part.min(axis=0).copy())
+        lab = torch.from_numpy((part.argmin(axis=0) + klo).astype(np.int32))
+        lab[torch.isinf(dmin)] = -1
+        allreduce_min_assignment(dmin, lab, dist)
+        exp_lab = D2.argmin(axis=0).astype(np.int32)
+        exp_lab[np.isinf(D2.min(axis=0))] = -1
+        ok = ok and np.array_equal(lab.numpy(), exp_lab) and np.array_equal(dmin.numpy(), D2.min(axis=0))
         q.put((rank, bool(ok)))
     finally:
         dist.destroy_process_group()

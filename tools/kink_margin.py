@@ -30,8 +30,8 @@ import numpy as np
 import torch
 import torch.nn as nn
 
-EPS = 1e-5          # |pre-activation| below which a float32 ReLU mask is considered undecidable (activations are O(1))
-COUPLED_TOL = 2e-4  # bound on the deviation a flipped unit elsewhere in the BatchNorm batch can cause
+EPS = 2e-6          # |pre-activation| below which a float32 ReLU mask is undecidable (activations are O(1); largest margin seen on a flipped edge: 5.4e-7)
+COUPLED_TOL = 1e-4  # bound on the deviation a flipped unit elsewhere in the BatchNorm batch can cause
 
 
 @torch.no_grad()

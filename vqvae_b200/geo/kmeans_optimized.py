@@ -60,11 +60,44 @@ def kpp_initialization_graph(W: sparse.spmatrix, K: int, seed: int = 42) -> List
     return centers
 
 
-def _labels_for(g, medoids):
-    """Insert the medoids in order -> (label int32 device, dmin32 device)."""
+def _shard_group(dist_group):
+    """(dist module, group, rank, world) when the K sources are to be split across ranks, else None.
+    Sharding is collective: every rank of the group must make the same call.  It is used when a group is passed
+    explicitly (the pipeline does) or, for the default group, when GEOCB_SHARD_SOURCES=1."""
+    import os
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        return None
+    if dist_group is None:
+        if os.environ.get("GEOCB_SHARD_SOURCES", "0") != "1":
+            return None
+        dist_group = dist.group.WORLD
+    world = dist.get_world_size(dist_group)
+    return (dist, dist_group, dist.get_rank(dist_group), world) if world > 1 else None
+
+
+def _labels_for(g, medoids, dist_group=None):
+    """Insert the medoids in order -> Voronoi state (label int32, dmin32 f32 on the device).
+
+    Multi-GPU: rank r inserts only medoids shard_range(K, r, world) -- independent sources, no chain --
+    and the per-rank (dmin32, label) pairs are combined with ONE allreduce-MIN over packed
+    (float32 bits << 32 | k) int64 keys: non-negative floats order like their bit patterns, so the minimum key is
+    the smallest distance and, on ties, the lowest k -- the reference's argmin rule (:100)."""
+    import torch
+    med = np.asarray(medoids, dtype=np.int64).tolist()
+    sh = _shard_group(dist_group)
     state = dg.VoronoiState(g)
-    for k, m in enumerate(np.asarray(medoids, dtype=np.int64).tolist()):
-        state.insert(int(m), code=k)
+    if sh is None:
+        for k, m in enumerate(med):
+            state.insert(int(m), code=k)
+        return state
+    dist, group, rank, world = sh
+    from ..sharding import shard_range, allreduce_min_assignment
+    lo, hi = shard_range(len(med), rank, world)
+    for k in range(lo, hi):
+        state.insert(int(med[k]), code=k)
+    allreduce_min_assignment(state.dmin32, state.label, dist, group)
+    state.count = len(med)
     return state
 
 
@@ -77,14 +110,14 @@ def _finish_assign(state, K):
     return assign
 
 
-def assign_points_to_medoids(W: sparse.spmatrix, medoids: np.ndarray) -> np.ndarray:
-    """argmin_k float32(D[k,n]) with the lowest k on ties (:77-106)."""
+def assign_points_to_medoids(W: sparse.spmatrix, medoids: np.ndarray, dist_group=None) -> np.ndarray:
+    """argmin_k float32(D[k,n]) with the lowest k on ties (:77-106).  `dist_group`: see _labels_for."""
     g = graph_to_device(W)
     K = len(medoids)
     if K == 0:
         raise ValueError("sources must be a non-empty sequence of node indices")
     print(f"[assign] {g.n} points to {K} medoids")  # :94
-    return _finish_assign(_labels_for(g, medoids), K)
+    return _finish_assign(_labels_for(g, medoids, dist_group), K)
 
 
 def _qe_from_dmin(dmin32) -> float:
@@ -92,14 +125,20 @@ def _qe_from_dmin(dmin32) -> float:
     return float(total) if used > 0 else float("inf")  # :133-134
 
 
-def compute_quantization_error(W: sparse.spmatrix, medoids: np.ndarray, assign: np.ndarray) -> float:
+def compute_quantization_error(W: sparse.spmatrix, medoids: np.ndarray, assign: np.ndarray, dist_group=None) -> float:
     """Sum of squared float32 geodesic distances to the assigned medoid (:109-138).
 
     `assign` may be any assignment, so D[assign[v], v] is gathered from true multi-source
-    distances, a chunk of sources at a time."""
+    distances, a chunk of sources at a time.  Multi-GPU: each rank runs its shard of the sources and the
+    picked distances (+inf elsewhere) are combined with an allreduce-MIN."""
     import torch
     g = graph_to_device(W)
     med = np.asarray(medoids, dtype=np.int64)
+    sh = _shard_group(dist_group)
+    k_lo, k_hi = 0, len(med)
+    if sh is not None:
+        from ..sharding import shard_range
+        k_lo, k_hi = shard_range(len(med), sh[2], sh[3])
     a = torch.as_tensor(np.asarray(assign, dtype=np.int64), device=g.indptr.device)
     picked = torch.full((g.n,), float("inf"), dtype=torch.float32, device=g.indptr.device)
     if g.nnz == 0:
@@ -108,16 +147,19 @@ def compute_quantization_error(W: sparse.spmatrix, medoids: np.ndarray, assign: 
         return _qe_from_dmin(picked)
     chunk = max(1, min(len(med), (256 << 20) // max(1, 4 * g.n)))
     cols = torch.arange(g.n, device=a.device)
-    for lo in range(0, len(med), chunk):
-        D = dg.sssp_multi(g, med[lo:lo + chunk])
+    for lo in range(k_lo, k_hi, chunk):
+        D = dg.sssp_multi(g, med[lo:min(lo + chunk, k_hi)])
         sel = (a >= lo) & (a < lo + D.shape[0])
         picked[sel] = D[(a[sel] - lo), cols[sel]]
+    if sh is not None:
+        sh[0].all_reduce(picked, op=sh[0].ReduceOp.MIN, group=sh[1])
     return _qe_from_dmin(picked)
 
 
-def fit_kmedoids_optimized(W: sparse.spmatrix, K: int = 512, init: str = "kpp", seed: int = 42,
+def fit_kmedoids_optimized(W: sparse.spmatrix, K: int = 512, init: str = "kpp", seed: int = 42, dist_group=None,
                            ) -> Tuple[np.ndarray, np.ndarray, float]:
-    """k-means++ (or random) seeding -> one assignment -> quantisation error (:141-183)."""
+    """k-means++ (or random) seeding -> one assignment -> quantisation error (:141-183).
+    Multi-GPU: the k-means++ chain is sequential and runs replicated; `init="random"` shards its K sources."""
     g = graph_to_device(W)
     N = g.n
     print(f"[kmedoids] N={N}, K={K}, edges={g.nnz}, avg_deg={g.nnz/max(1,N):.1f}")  # :164
@@ -130,7 +172,7 @@ def fit_kmedoids_optimized(W: sparse.spmatrix, K: int = 512, init: str = "kpp", 
     elif init == "random":
         rng = np.random.RandomState(seed)
         medoids = rng.choice(N, size=min(K, N), replace=False).astype(int)  # :170-171
-        state = _labels_for(g, medoids)
+        state = _labels_for(g, medoids, dist_group)
     else:
         raise ValueError("init must be 'kpp' or 'random'")  # :173
     print(f"[assign] {N} points to {len(medoids)} medoids")

@@ -17,6 +17,7 @@ import torch
 
 from . import _lib
 from . import device_graph as dg
+from .sharding import shard_range, all_gather_rows  # noqa: F401  (re-exported)
 from .geo.knn_graph_optimized import knn_graph_device
 from .geo.riemannian_metric import edge_lengths_device
 from .geo.kmeans_optimized import fit_kmedoids_optimized
@@ -27,28 +28,6 @@ def _dist_info(group):
     if group is None and not (dist.is_available() and dist.is_initialized()):
         return None, 0, 1
     return dist, dist.get_rank(group), dist.get_world_size(group)
-
-
-def shard_range(total, rank, world, multiple=1):
-    """Contiguous [lo,hi) of `total` items for `rank`, boundaries at multiples of `multiple`."""
-    units = -(-total // multiple)
-    per, extra = divmod(units, world)
-    lo_u = rank * per + min(rank, extra)
-    hi_u = lo_u + per + (1 if rank < extra else 0)
-    return min(lo_u * multiple, total), min(hi_u * multiple, total)
-
-
-def all_gather_rows(x, total_rows, world, rank, group, dist, multiple=1):
-    """Concatenate per-rank row shards (shard_range layout) into the full tensor on every rank."""
-    if world == 1:
-        return x
-    sizes = [shard_range(total_rows, r, world, multiple) for r in range(world)]
-    mx = max(hi - lo for lo, hi in sizes)
-    pad = torch.zeros((mx,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
-    pad[: x.shape[0]] = x
-    bufs = [torch.empty_like(pad) for _ in range(world)]
-    dist.all_gather(bufs, pad, group=group)
-    return torch.cat([b[: hi - lo] for b, (lo, hi) in zip(bufs, sizes)], 0)
 
 
 @dataclass
@@ -86,10 +65,15 @@ class _Timer:
 
 
 def build_codebook_device(z4: torch.Tensor, decoder, k=20, sym="union", K=512, init="kpp", seed=42, batch_size=512,
-                          group=None, verbose=True) -> BuildResult:
-    """Everything between loading the inputs and writing the artifacts."""
+                          group=None, verbose=True, distributed=True) -> BuildResult:
+    """Everything between loading the inputs and writing the artifacts.
+    distributed=False runs the whole build on this rank alone even under torch.distributed (reference runs for the
+    sharded-vs-single digest checks)."""
     dev = _lib.require_cuda()
-    dist, rank, world = _dist_info(group)
+    dist, rank, world = _dist_info(group) if distributed else (None, 0, 1)
+    shard_group = None
+    if world > 1:
+        shard_group = group if group is not None else dist.group.WORLD
     N, C, H, Wd = z4.shape
     tm = _Timer()
     tm("h2d")
@@ -149,12 +133,12 @@ def build_codebook_device(z4: torch.Tensor, decoder, k=20, sym="union", K=512, i
     # ---- K-medoids (:70) ----
     tm("kmedoids")
     if verbose and rank == 0:
-        medoids, assign, qe = fit_kmedoids_optimized(g_lcc, K=K, init=init, seed=seed)
+        medoids, assign, qe = fit_kmedoids_optimized(g_lcc, K=K, init=init, seed=seed, dist_group=shard_group)
     else:
         import contextlib
         import io
         with contextlib.redirect_stdout(io.StringIO()):
-            medoids, assign, qe = fit_kmedoids_optimized(g_lcc, K=K, init=init, seed=seed)
+            medoids, assign, qe = fit_kmedoids_optimized(g_lcc, K=K, init=init, seed=seed, dist_group=shard_group)
     tm("codes")
     codes = np.full(M, -1, dtype=np.int32)  # :74-76
     codes[mask.cpu().numpy().astype(bool)] = assign
