@@ -37,8 +37,9 @@ int geocb_device_info(int* sm_count, int* cc);
  * For query rows [q_lo,q_hi) of z[M,d] (row-major f32) find the kq nearest rows
  * of z (self included), ordered by (exact fp64 squared distance, index).
  *   pass 1: filter  |b|^2 - 2ab  over all candidates, keeping the best kq+slack per row:
- *           d <= 16 and kq <= 26: tcgen05 tensor cores, 3xTF32 split (fp32-grade scores,
- *           csrc/knn_tc.cu; env GEOCB_KNN_TC=0 disables); otherwise fused fp32 FFMA2 tiles.
+ *           d <= 64 and kq <= 26: tcgen05 tensor cores, 3xTF32 split (fp32-grade scores,
+ *           csrc/knn_tc.cu; env GEOCB_KNN_TC=0 disables); otherwise fused fp32 FFMA2 tiles (d <= 64, kq <= 56)
+ *           or, beyond that, the exact fp64 kernel for every row.
  *   pass 2: exact fp64 re-rank of the candidates; rows whose filter margin is
  *           not provably safe are redone by an exact fp64 brute-force kernel.
  *   The result never depends on which filter ran.
@@ -46,6 +47,14 @@ int geocb_device_info(int* sm_count, int* cc);
  * n_unsafe (device int32[1], nullable): rows that took the exact brute-force path. */
 int geocb_knn_topk(const float* z, int64_t M, int d, int64_t q_lo, int64_t q_hi, int kq,
                    int32_t* out_idx, float* out_dist, int32_t* n_unsafe, void* stream);
+
+/* Same search with SEPARATE query and candidate sets: queries[nq,d] against cand[M,d] (no self to drop).
+ * kq = 1 is the downstream "nearest medoid" assignment of held-out latents to the K codebook entries
+ * (src/eval/evaluate_codebook_health.py:13-26, evaluate_quantization_loss.py:37-50: d2.argmin(dim=1)), which the
+ * reference ranks in float32 (a2 + b2 - 2ab); here the order is by exact fp64 squared distance, ties -> lowest index,
+ * so results differ from the reference only where its float32 scores tie or cross within rounding. */
+int geocb_knn_query(const float* queries, int64_t nq, const float* cand, int64_t M, int d, int kq,
+                    int32_t* out_idx, float* out_dist, int32_t* n_unsafe, void* stream);
 
 /* ------------------------------------------------- symmetrise -> CSR -----
  * replaces scipy csr_matrix(...) ; W.maximum/minimum(W.T) ; setdiag(0) ;

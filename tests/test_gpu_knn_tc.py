@@ -1,0 +1,63 @@
+"""tcgen05 kNN filter for every padded dimension (16 / 32 / 64) and the query-vs-candidate entry point
+(geocb_knn_query): index lists identical to sklearn's brute search / to an exact float64 argmin."""
+import numpy as np
+import pytest
+import torch
+
+import geo_oracle as oracle
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dg():
+    assert torch.cuda.is_available()
+    from vqvae_b200 import device_graph, _lib
+    _lib.load()
+    return device_graph
+
+
+@pytest.mark.parametrize("d,n,k", [(16, 5000, 20), (24, 4000, 20), (32, 6000, 20), (33, 3000, 10), (48, 3000, 25), (64, 5000, 20)])
+def test_knn_tc_dims_vs_sklearn(dg, d, n, k):
+    """d <= 64 and k+1 <= 26 take the tensor-core filter (no row may need the exact fallback for iid data)."""
+    from sklearn.neighbors import NearestNeighbors
+    z = np.random.RandomState(d).randn(n, d).astype(np.float32)
+    zt = torch.from_numpy(z).cuda()
+    idx, dist, nun = dg.knn_topk(zt, k + 1)
+    dref, iref = NearestNeighbors(n_neighbors=k + 1, algorithm="brute").fit(z).kneighbors(z)
+    assert np.array_equal(idx.cpu().numpy(), iref)
+    np.testing.assert_allclose(dist.cpu().numpy(), dref, rtol=2e-6, atol=1e-6)
+    assert int(nun.item()) <= n // 100
+    # a query slice in the middle of the range (the multi-GPU sharding path)
+    idx2, _, _ = dg.knn_topk(zt, k + 1, 1000, 1777)
+    assert np.array_equal(idx2.cpu().numpy(), iref[1000:1777])
+
+
+@pytest.mark.parametrize("d,K", [(16, 512), (32, 512), (64, 1024), (128, 64)])
+def test_nearest_medoid_assign(dg, d, K):
+    """Downstream assignment of held-out latents (src/eval/evaluate_codebook_health.py:13-26): the code is the exactly
+    nearest medoid; equal to a float64 argmin, and to the reference's float32 argmin except at float32 near-ties."""
+    from vqvae_b200.eval import nearest_medoid_assign, decode_codes, valid_code_rows
+    rs = np.random.RandomState(K + d)
+    z = torch.from_numpy(rs.randn(20000, d).astype(np.float32))
+    zm = z[rs.choice(20000, K, replace=False)].clone()
+    codes = nearest_medoid_assign(z, zm)
+    assert codes.dtype == torch.long and codes.shape == (20000,) and codes.device.type == "cpu"
+    d2 = ((z.double()[:, None, :] - zm.double()[None, :, :]) ** 2).sum(-1) if K * 20000 * d < 3e8 else None
+    if d2 is None:
+        d2 = (z.double() ** 2).sum(1, keepdim=True) + (zm.double() ** 2).sum(1)[None] - 2.0 * z.double() @ zm.double().t()
+        agree = (codes == d2.argmin(1)).float().mean().item()
+        assert agree > 0.9999
+    else:
+        assert torch.equal(codes, d2.argmin(1))
+    # reference formula in float32
+    ref = ((z ** 2).sum(1, keepdim=True) + (zm ** 2).sum(1).view(1, -1) - 2.0 * z @ zm.t()).argmin(1)
+    assert (codes == ref).float().mean().item() > 0.999
+    assert torch.equal(codes[torch.from_numpy(np.isin(np.arange(20000), []))], torch.empty(0, dtype=torch.long))
+    # artifact conventions
+    grid = codes[:64].reshape(4, 4, 4)
+    assert decode_codes(grid, zm).shape == (4, d, 4, 4)
+    assert torch.equal(decode_codes(grid, zm)[1, :, 2, 3], zm[grid[1, 2, 3]])
+    c = np.zeros((5, 2, 2), np.int32)
+    c[3, 1, 0] = -1
+    assert valid_code_rows(c).tolist() == [True, True, True, False, True]

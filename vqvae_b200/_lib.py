@@ -26,6 +26,7 @@ SIGNATURES = {
     "geocb_last_error": (C.c_char_p, []),
     "geocb_device_info": (_int, [C.POINTER(_int), C.POINTER(_int)]),
     "geocb_knn_topk": (_int, [_p, _i64, _int, _i64, _i64, _int, _p, _p, _p, _p]),
+    "geocb_knn_query": (_int, [_p, _i64, _p, _i64, _int, _int, _p, _p, _p, _p]),
     "geocb_sym_count": (_int, [_p, _p, _i64, _int, _int, _p, _pi64, _p]),
     "geocb_sym_fill": (_int, [_p, _p, _i64, _int, _int, _p, _p, _p, _p]),
     "geocb_upper_count": (_int, [_p, _p, _i64, _p, _pi64, _p]),

@@ -85,10 +85,10 @@ __global__ void knn_prep_kernel(const float* z, int64_t M, int d, int dpad, int6
 
 // ------------------------------------------------------------------ pass 1 ----
 template <int DPAD, int RQ, int L>
-__global__ void __launch_bounds__(kFilterThreads) knn_filter_kernel(const float* __restrict__ z, int d,
+__global__ void __launch_bounds__(kFilterThreads) knn_filter_kernel(const float* __restrict__ zq, int d,
                                                                     const float* __restrict__ zt,
                                                                     const float* __restrict__ nrm, int64_t Mp,
-                                                                    int64_t q_lo, int64_t nq, int32_t* cand_idx,
+                                                                    int64_t nq, int32_t* cand_idx,
                                                                     float* cand_thr) {
     constexpr int TILE_C = kTileBytes / (DPAD * 4);
     constexpr int NT = kFilterThreads * RQ;
@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(kFilterThreads) knn_filter_kernel(const float*
 #pragma unroll
     for (int r = 0; r < RQ; ++r) {
         const int64_t q = (int64_t)blockIdx.x * NT + r * kFilterThreads + tid;
-        const float* src = z + (q_lo + (q < nq ? q : 0)) * d;
+        const float* src = zq + (q < nq ? q : 0) * d;
 #pragma unroll
         for (int i = 0; i < DPAD; ++i) {
             float v = i < d ? -2.0f * src[i] : 0.f;
@@ -217,7 +217,7 @@ __device__ __forceinline__ bool key_less(double d0, int i0, double d1, int i1) {
 }
 
 template <int L>
-__global__ void knn_rerank_kernel(const float* __restrict__ z, int64_t M, int d, int64_t q_lo, int64_t nq, int kq,
+__global__ void knn_rerank_kernel(const float* __restrict__ z, const float* __restrict__ zq, int64_t M, int d, int64_t nq, int kq,
                                   const int32_t* cand_idx, const float* cand_thr, const unsigned int* max_nrm_bits,
                                   double eps_unit, int32_t* out_idx, float* out_dist, int32_t* unsafe_rows,
                                   int32_t* n_unsafe) {
@@ -225,7 +225,7 @@ __global__ void knn_rerank_kernel(const float* __restrict__ z, int64_t M, int d,
     const int64_t q = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (q >= nq) return;
-    const float* a = z + (q_lo + q) * d;
+    const float* a = zq + q * d;
     double d2[PER];
     int id[PER];
     int nvalid = 0;
@@ -289,7 +289,7 @@ __global__ void knn_rerank_kernel(const float* __restrict__ z, int64_t M, int d,
 
 // ------------------------------------------------------------------ pass 3 ----
 // exact fp64 selection for one query per CTA: kq rounds of "smallest key greater than the last one".
-__global__ void knn_exact_kernel(const float* __restrict__ z, int64_t M, int d, int64_t q_lo, int kq,
+__global__ void knn_exact_kernel(const float* __restrict__ z, const float* __restrict__ zq, int64_t M, int d, int kq,
                                  const int32_t* rows, const int32_t* n_rows, int all_rows, int32_t* out_idx,
                                  float* out_dist) {
     const int nr = all_rows ? all_rows : *n_rows;
@@ -299,7 +299,7 @@ __global__ void knn_exact_kernel(const float* __restrict__ z, int64_t M, int d, 
     __shared__ int last_i;
     for (int rr = blockIdx.x; rr < nr; rr += gridDim.x) {
         const int64_t q = all_rows ? rr : rows[rr];
-        const float* a = z + (q_lo + q) * d;
+        const float* a = zq + q * d;
         if (threadIdx.x == 0) {
             last_d = -1.0;
             last_i = -1;
@@ -341,7 +341,7 @@ __global__ void knn_exact_kernel(const float* __restrict__ z, int64_t M, int d, 
 }
 
 template <int DPAD, int RQ, int L>
-int launch_filter(const float* z, int d, const float* zt, const float* nrm, int64_t Mp, int64_t q_lo, int64_t nq,
+int launch_filter(const float* zq, int d, const float* zt, const float* nrm, int64_t Mp, int64_t nq,
                   int32_t* cand_idx, float* cand_thr, cudaStream_t st) {
     constexpr int TILE_C = kTileBytes / (DPAD * 4);
     constexpr int NT = kFilterThreads * RQ;
@@ -349,20 +349,20 @@ int launch_filter(const float* z, int d, const float* zt, const float* nrm, int6
     auto kern = knn_filter_kernel<DPAD, RQ, L>;
     CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const unsigned grid = (unsigned)((nq + NT - 1) / NT);
-    kern<<<grid, kFilterThreads, smem, st>>>(z, d, zt, nrm, Mp, q_lo, nq, cand_idx, cand_thr);
+    kern<<<grid, kFilterThreads, smem, st>>>(zq, d, zt, nrm, Mp, nq, cand_idx, cand_thr);
     KERNEL_CHECK();
     return 0;
 }
 
 template <int L>
-int dispatch_filter(int dpad, const float* z, int d, const float* zt, const float* nrm, int64_t Mp, int64_t q_lo,
+int dispatch_filter(int dpad, const float* zq, int d, const float* zt, const float* nrm, int64_t Mp,
                     int64_t nq, int32_t* cand_idx, float* cand_thr, cudaStream_t st) {
     switch (dpad) {
-        case 4: return launch_filter<4, 2, L>(z, d, zt, nrm, Mp, q_lo, nq, cand_idx, cand_thr, st);
-        case 8: return launch_filter<8, 2, L>(z, d, zt, nrm, Mp, q_lo, nq, cand_idx, cand_thr, st);
-        case 16: return launch_filter<16, 2, L>(z, d, zt, nrm, Mp, q_lo, nq, cand_idx, cand_thr, st);
-        case 32: return launch_filter<32, 1, L>(z, d, zt, nrm, Mp, q_lo, nq, cand_idx, cand_thr, st);
-        case 64: return launch_filter<64, 1, L>(z, d, zt, nrm, Mp, q_lo, nq, cand_idx, cand_thr, st);
+        case 4: return launch_filter<4, 2, L>(zq, d, zt, nrm, Mp, nq, cand_idx, cand_thr, st);
+        case 8: return launch_filter<8, 2, L>(zq, d, zt, nrm, Mp, nq, cand_idx, cand_thr, st);
+        case 16: return launch_filter<16, 2, L>(zq, d, zt, nrm, Mp, nq, cand_idx, cand_thr, st);
+        case 32: return launch_filter<32, 1, L>(zq, d, zt, nrm, Mp, nq, cand_idx, cand_thr, st);
+        case 64: return launch_filter<64, 1, L>(zq, d, zt, nrm, Mp, nq, cand_idx, cand_thr, st);
     }
     return GEOCB_ERR_UNSUPPORTED;
 }
@@ -383,15 +383,12 @@ struct Scratch {
 };
 }  // namespace
 
-GEOCB_API int geocb_knn_topk(const float* z, int64_t M, int d, int64_t q_lo, int64_t q_hi, int kq, int32_t* out_idx,
-                             float* out_dist, int32_t* n_unsafe, void* stream) {
-    ARG_CHECK(z && out_idx && M > 0 && d > 0 && q_lo >= 0 && q_hi <= M && q_lo < q_hi && kq > 0 && kq <= M);
-    ARG_CHECK(M < (1LL << 31) - 2048);
-    cudaStream_t st = (cudaStream_t)stream;
+// queries zq[nq][d] against candidates z[M][d] (zq may point into z)
+static int knn_query_impl(const float* z, const float* zq, int64_t M, int d, int64_t nq, int kq, int32_t* out_idx,
+                          float* out_dist, int32_t* n_unsafe, cudaStream_t st) {
     DevInfo di;
     int rc = geocb_devinfo(&di);
     if (rc) return rc;
-    const int64_t nq = q_hi - q_lo;
     CU_TRY(cudaMemsetAsync(out_idx, 0xFF, (size_t)nq * kq * 4, st));
     Scratch sx(st);
     int32_t* unsafe_cnt = nullptr;
@@ -403,25 +400,25 @@ GEOCB_API int geocb_knn_topk(const float* z, int64_t M, int d, int64_t q_lo, int
     const bool fast = dpad <= 64 && kq <= 56;
     const double eps_ffma = (2.0 * d + 8.0) * 5.9604644775390625e-08 * 1.01;
     const char* tc_env = getenv("GEOCB_KNN_TC");
-    const bool use_tc = d <= 16 && kq <= 26 && !(tc_env && tc_env[0] == '0');
+    const bool use_tc = d <= 64 && kq <= 26 && !(tc_env && tc_env[0] == '0');
     if (use_tc) {
         // tcgen05 filter (knn_tc.cu) -> same exact re-rank / certificate / fallback as the FFMA2 path
-        const int64_t Mp = knn_tc_padded_candidates(M), nqp = knn_tc_padded_queries(nq);
+        const int64_t Mp = knn_tc_padded_candidates(M), nqp = knn_tc_padded_queries(nq, d);
         float *bimg, *aimg, *cand_thr;
         int32_t *cand_idx, *unsafe_rows;
-        if ((rc = sx.alloc((void**)&bimg, (size_t)knn_tc_image_floats(Mp) * 4)) ||
-            (rc = sx.alloc((void**)&aimg, (size_t)knn_tc_image_floats(nqp) * 4)) ||
+        if ((rc = sx.alloc((void**)&bimg, (size_t)knn_tc_image_floats(Mp, d) * 4)) ||
+            (rc = sx.alloc((void**)&aimg, (size_t)knn_tc_image_floats(nqp, d) * 4)) ||
             (rc = sx.alloc((void**)&cand_idx, (size_t)nq * 32 * 4)) || (rc = sx.alloc((void**)&cand_thr, (size_t)nq * 4)) ||
             (rc = sx.alloc((void**)&unsafe_rows, (size_t)nq * 4)))
             return rc;
         unsigned int* max_nrm = (unsigned int*)(unsafe_cnt + 1);
-        if ((rc = knn_filter_tc(z, M, d, q_lo, nq, bimg, aimg, max_nrm, cand_idx, cand_thr, st))) return rc;
+        if ((rc = knn_filter_tc(z, zq, M, d, nq, bimg, aimg, max_nrm, cand_idx, cand_thr, st))) return rc;
         const unsigned rb = (unsigned)((nq * 32 + 255) / 256);
-        knn_rerank_kernel<32><<<rb, 256, 0, st>>>(z, M, d, q_lo, nq, kq, cand_idx, cand_thr, max_nrm,
+        knn_rerank_kernel<32><<<rb, 256, 0, st>>>(z, zq, M, d, nq, kq, cand_idx, cand_thr, max_nrm,
                                                    7.62939453125e-06 /* 2^-17 */, out_idx, out_dist, unsafe_rows,
                                                    unsafe_cnt);
         KERNEL_CHECK();
-        knn_exact_kernel<<<di.sm_count * 4, 256, 0, st>>>(z, M, d, q_lo, kq, unsafe_rows, unsafe_cnt, 0, out_idx,
+        knn_exact_kernel<<<di.sm_count * 4, 256, 0, st>>>(z, zq, M, d, kq, unsafe_rows, unsafe_cnt, 0, out_idx,
                                                            out_dist);
         KERNEL_CHECK();
     } else if (fast) {
@@ -436,23 +433,23 @@ GEOCB_API int geocb_knn_topk(const float* z, int64_t M, int d, int64_t q_lo, int
         unsigned int* max_nrm = (unsigned int*)(unsafe_cnt + 1);
         knn_prep_kernel<<<(unsigned)((Mp + 255) / 256), 256, 0, st>>>(z, M, d, dpad, Mp, zt, nrm, max_nrm);
         KERNEL_CHECK();
-        rc = L == 32 ? dispatch_filter<32>(dpad, z, d, zt, nrm, Mp, q_lo, nq, cand_idx, cand_thr, st)
-                     : dispatch_filter<64>(dpad, z, d, zt, nrm, Mp, q_lo, nq, cand_idx, cand_thr, st);
+        rc = L == 32 ? dispatch_filter<32>(dpad, zq, d, zt, nrm, Mp, nq, cand_idx, cand_thr, st)
+                     : dispatch_filter<64>(dpad, zq, d, zt, nrm, Mp, nq, cand_idx, cand_thr, st);
         if (rc) return rc;
         const unsigned rb = (unsigned)((nq * 32 + 255) / 256);
         if (L == 32)
-            knn_rerank_kernel<32><<<rb, 256, 0, st>>>(z, M, d, q_lo, nq, kq, cand_idx, cand_thr, max_nrm, eps_ffma,
+            knn_rerank_kernel<32><<<rb, 256, 0, st>>>(z, zq, M, d, nq, kq, cand_idx, cand_thr, max_nrm, eps_ffma,
                                                        out_idx, out_dist, unsafe_rows, unsafe_cnt);
         else
-            knn_rerank_kernel<64><<<rb, 256, 0, st>>>(z, M, d, q_lo, nq, kq, cand_idx, cand_thr, max_nrm, eps_ffma,
+            knn_rerank_kernel<64><<<rb, 256, 0, st>>>(z, zq, M, d, nq, kq, cand_idx, cand_thr, max_nrm, eps_ffma,
                                                        out_idx, out_dist, unsafe_rows, unsafe_cnt);
         KERNEL_CHECK();
-        knn_exact_kernel<<<di.sm_count * 4, 256, 0, st>>>(z, M, d, q_lo, kq, unsafe_rows, unsafe_cnt, 0, out_idx,
+        knn_exact_kernel<<<di.sm_count * 4, 256, 0, st>>>(z, zq, M, d, kq, unsafe_rows, unsafe_cnt, 0, out_idx,
                                                            out_dist);
         KERNEL_CHECK();
     } else {
         ARG_CHECK(nq < (1LL << 31));
-        knn_exact_kernel<<<di.sm_count * 4, 256, 0, st>>>(z, M, d, q_lo, kq, nullptr, nullptr, (int)nq, out_idx,
+        knn_exact_kernel<<<di.sm_count * 4, 256, 0, st>>>(z, zq, M, d, kq, nullptr, nullptr, (int)nq, out_idx,
                                                            out_dist);
         KERNEL_CHECK();
         // report every row as having taken the exact path
@@ -461,4 +458,18 @@ GEOCB_API int geocb_knn_topk(const float* z, int64_t M, int d, int64_t q_lo, int
     }
     if (n_unsafe) CU_TRY(cudaMemcpyAsync(n_unsafe, unsafe_cnt, 4, cudaMemcpyDeviceToDevice, st));
     return 0;
+}
+
+GEOCB_API int geocb_knn_topk(const float* z, int64_t M, int d, int64_t q_lo, int64_t q_hi, int kq, int32_t* out_idx,
+                             float* out_dist, int32_t* n_unsafe, void* stream) {
+    ARG_CHECK(z && out_idx && M > 0 && d > 0 && q_lo >= 0 && q_hi <= M && q_lo < q_hi && kq > 0 && kq <= M);
+    ARG_CHECK(M < (1LL << 31) - 2048);
+    return knn_query_impl(z, z + q_lo * d, M, d, q_hi - q_lo, kq, out_idx, out_dist, n_unsafe, (cudaStream_t)stream);
+}
+
+GEOCB_API int geocb_knn_query(const float* queries, int64_t nq, const float* cand, int64_t M, int d, int kq,
+                              int32_t* out_idx, float* out_dist, int32_t* n_unsafe, void* stream) {
+    ARG_CHECK(queries && cand && out_idx && nq > 0 && M > 0 && d > 0 && kq > 0 && kq <= M);
+    ARG_CHECK(M < (1LL << 31) - 2048 && nq < (1LL << 31));
+    return knn_query_impl(cand, queries, M, d, nq, kq, out_idx, out_dist, n_unsafe, (cudaStream_t)stream);
 }

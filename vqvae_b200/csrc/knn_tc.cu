@@ -1,4 +1,4 @@
-// knn_tc.cu -- kNN filter pass on the 5th-generation tensor cores (tcgen05 + TMEM), d <= 16.
+// knn_tc.cu -- kNN filter pass on the 5th-generation tensor cores (tcgen05 + TMEM), d <= 64.
 //
 // Replaces pass 1 of knn.cu (the fp32 FFMA2 filter) for the reference's kNN query
 // (src/geo/knn_graph_optimized.py:39-42).  Only the contraction runs on tensor cores:
@@ -18,20 +18,32 @@
 //   warps 0-7      : epilogue -- thread = query row: tcgen05.ld 32 scores at a time, a min-tree screens them
 //                    against the row's current threshold, the rare survivors enter the row's L-entry list.
 // Output is the same (cand_idx, cand_thr) pair knn.cu's exact fp64 re-rank + certificate consume.
+//
+// The row image scales with the padded dimension DP in {16, 32, 64}: [hi DP | lo DP | norm/ones 8] floats, 3*DP/8 + 1
+// MMAs per tile pair (7 / 13 / 25).  Shared memory decides the shape: DP=16: two A tiles, 4 B stages; DP=32: two A
+// tiles, 2 stages; DP=64: ONE A tile (68 KB) and the B tile staged in two K-halves (hi | lo+norm, 3 half stages).
 #include "common.cuh"
 #include "knn_tc.cuh"
 
 namespace {
 
-constexpr int kRowFloats = 40;              // floats per operand row image
-constexpr int kKGroups = kRowFloats / 4;    // 16-byte K-groups per row
 constexpr int kTileRows = 128;
 constexpr int kLBO = kTileRows * 16;        // bytes between K-groups
-constexpr int kTileBytes = kKGroups * kLBO; // 20480
-constexpr int kStages = 4;
 constexpr int kL = 32;                      // list length (kq <= 26)
-constexpr int kRowsPerCta = 256;
 constexpr int kThreads = 320;
+
+template <int DP_, int ATILES_, int STAGES_, int NSUB_>
+struct Cfg {
+    static constexpr int DP = DP_, ATILES = ATILES_, STAGES = STAGES_, NSUB = NSUB_;
+    static constexpr int kRowFloats = 2 * DP + 8;        // floats per operand row image
+    static constexpr int kKGroups = kRowFloats / 4;      // 16-byte K-groups per row
+    static constexpr int kTileBytes = kKGroups * kLBO;   // 20480 / 36864 / 69632
+    static constexpr int kRowsPerCta = ATILES * kTileRows;
+    // B sub-tiles (K-group ranges): one, or [hi) and [lo + norm)
+    static constexpr int kSplit = NSUB == 1 ? kKGroups : DP / 4;
+    static constexpr int kStageBytes = (NSUB == 1 ? kKGroups : (kKGroups - DP / 4)) * kLBO;
+    static constexpr int kSteps = 3 * DP / 8 + 1;
+};
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
@@ -111,35 +123,55 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 
 // byte offset of element (row r, float k) inside a 128-row operand tile image
 __device__ __forceinline__ int img_off(int r, int k) { return (k >> 2) * kLBO + (r >> 3) * 128 + (r & 7) * 16 + (k & 3) * 4; }
+// K-group pairs (A kg, B kg) of MMA step t for padded dimension DP: steps are grouped by the B sub-tile they read:
+// first every step on B's hi part (hi.hi and lo.hi per 8-float chunk), then hi.lo per chunk, then ones.norm.
+template <int DP>
+__device__ __forceinline__ void mma_step(int t, int& akg, int& bkg) {
+    constexpr int C = DP / 8;
+    if (t < 2 * C) {
+        const int j = t >> 1;
+        akg = (t & 1) ? DP / 4 + 2 * j : 2 * j;
+        bkg = 2 * j;
+    } else if (t < 3 * C) {
+        const int j = t - 2 * C;
+        akg = 2 * j;
+        bkg = DP / 4 + 2 * j;
+    } else {
+        akg = bkg = DP / 2;
+    }
+}
 
 // ------------------------------------------------------------------ prep ----
-// one thread per (row, K-group): writes the candidate image (all M rows, padded to whole tiles) and, for rows
-// inside [q_lo, q_lo+nq_pad), the query image.  Pad candidates get a huge finite norm so they are never kept.
-__global__ void knn_tc_prep_kernel(const float* __restrict__ z, int64_t M, int d, int64_t Mp, int64_t q_lo, int64_t nq,
-                                   int64_t nq_pad, float* bimg, float* aimg, unsigned int* max_nrm_bits) {
+// one thread per (row, K-group): writes the candidate image (all M rows, padded to whole tiles) and the query image
+// (nq rows of zq, padded to whole CTAs).  Pad candidates get a huge finite norm so they are never kept.
+__global__ void knn_tc_prep_kernel(const float* __restrict__ z, const float* __restrict__ zq, int64_t M, int d, int dp,
+                                   int64_t Mp, int64_t nq, int64_t nq_pad, float* bimg, float* aimg,
+                                   unsigned int* max_nrm_bits) {
+    const int kgroups = (2 * dp + 8) / 4, hi_groups = dp / 4;
+    const int64_t tile_floats = (int64_t)kgroups * kLBO / 4;
     const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t row = gid / kKGroups;
-    const int kg = (int)(gid % kKGroups);
+    const int64_t row = gid / kgroups;
+    const int kg = (int)(gid % kgroups);
     const bool is_b = row < Mp;
     const int64_t qrow = row - Mp;  // rows >= Mp enumerate the query image
     if (!is_b && qrow >= nq_pad) return;
-    const int64_t src = is_b ? row : q_lo + qrow;
     const bool live = is_b ? row < M : qrow < nq;
+    const float* src = is_b ? z + row * d : zq + qrow * d;
     float out[4] = {0.f, 0.f, 0.f, 0.f};
-    if (kg < 8) {  // hi (kg 0-3) / lo (kg 4-7) parts of 4 coordinates
-        const int c0 = (kg & 3) * 4;
+    if (kg < 2 * hi_groups) {  // hi (first dp/4 groups) / lo (next dp/4 groups) parts of 4 coordinates
+        const int c0 = (kg % hi_groups) * 4;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            float v = (live && c0 + i < d) ? z[src * d + c0 + i] : 0.f;
+            float v = (live && c0 + i < d) ? src[c0 + i] : 0.f;
             if (!is_b) v *= -2.0f;
             const float hi = to_tf32(v);
-            out[i] = kg < 4 ? hi : v - hi;
+            out[i] = kg < hi_groups ? hi : v - hi;
         }
-    } else if (kg == 8) {
+    } else if (kg == 2 * hi_groups) {
         if (is_b) {
             float s = 0.f;
             if (live) {
-                for (int i = 0; i < d; ++i) s = __fmaf_rn(z[src * d + i], z[src * d + i], s);
+                for (int i = 0; i < d; ++i) s = __fmaf_rn(src[i], src[i], s);
                 atomicMax(max_nrm_bits, __float_as_uint(s));
             } else {
                 s = 3.0e38f;
@@ -154,34 +186,37 @@ __global__ void knn_tc_prep_kernel(const float* __restrict__ z, int64_t M, int d
     }
     const int64_t tile = (is_b ? row : qrow) / kTileRows;
     const int r = (int)((is_b ? row : qrow) % kTileRows);
-    float* base = (is_b ? bimg : aimg) + tile * (kTileBytes / 4);
+    float* base = (is_b ? bimg : aimg) + tile * tile_floats;
     *(float4*)((char*)base + img_off(r, kg * 4)) = make_float4(out[0], out[1], out[2], out[3]);
 }
 
 // ------------------------------------------------------------------ filter ----
+template <int STAGES>
 struct alignas(8) TcBars {
-    uint64_t a_full, full[kStages], empty[kStages], tmem_full[2], tmem_empty[2];
+    uint64_t a_full, full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2];
     uint32_t tmem_base;
 };
 
+template <class C>
 __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float* __restrict__ aimg,
                                                                      const float* __restrict__ bimg, int64_t Mp,
                                                                      int64_t nq, int32_t* cand_idx, float* cand_thr) {
+    constexpr int kTileBytes = C::kTileBytes, kStages = C::STAGES, kRowsPerCta = C::kRowsPerCta, NSUB = C::NSUB;
     extern __shared__ __align__(1024) unsigned char smem[];
-    unsigned char* a_s = smem;                              // 2 A tiles
-    unsigned char* b_s = smem + 2 * kTileBytes;             // kStages B tiles
-    float* sc = (float*)(b_s + kStages * kTileBytes);       // [kL][256] list scores
-    int32_t* ix = (int32_t*)(sc + kL * kRowsPerCta);        // [kL][256] list indices
-    TcBars* bars = (TcBars*)(ix + kL * kRowsPerCta);
+    unsigned char* a_s = smem;                                   // ATILES A tiles
+    unsigned char* b_s = smem + C::ATILES * kTileBytes;          // kStages B (sub-)tiles
+    float* sc = (float*)(b_s + kStages * C::kStageBytes);        // [kL][rows] list scores
+    int32_t* ix = (int32_t*)(sc + kL * kRowsPerCta);             // [kL][rows] list indices
+    TcBars<kStages>* bars = (TcBars<kStages>*)(ix + kL * kRowsPerCta);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int64_t nchunks = Mp / kTileRows;
-    const int64_t tile0 = (int64_t)blockIdx.x * 2;  // first of this CTA's two A tiles
+    const int64_t tile0 = (int64_t)blockIdx.x * C::ATILES;  // first of this CTA's A tiles
 
     if (tid == 0) {
         mbar_init(&bars->a_full, 1);
         for (int s = 0; s < kStages; ++s) mbar_init(&bars->full[s], 1), mbar_init(&bars->empty[s], 1);
-        for (int b = 0; b < 2; ++b) mbar_init(&bars->tmem_full[b], 1), mbar_init(&bars->tmem_empty[b], 8);
+        for (int b = 0; b < 2; ++b) mbar_init(&bars->tmem_full[b], 1), mbar_init(&bars->tmem_empty[b], 4 * C::ATILES);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 9) {  // one warp allocates all 512 TMEM columns (1 CTA per SM: the shared-memory footprint forces it)
@@ -195,15 +230,19 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
     const uint32_t tmem_base = *(volatile uint32_t*)&bars->tmem_base;
 
     if (warp == 8) {
-        // ===== TMA producer =====
+        // ===== TMA producer: A tiles once, then the ring of B (sub-)tiles =====
         if (lane == 0) {
-            mbar_expect_tx(&bars->a_full, 2 * kTileBytes);
-            tma_load_1d(a_s, aimg + tile0 * (kTileBytes / 4), 2 * kTileBytes, &bars->a_full);
-            for (int64_t c = 0; c < nchunks; ++c) {
-                const int st = (int)(c % kStages);
-                mbar_wait(&bars->empty[st], (uint32_t)(((c / kStages) & 1) ^ 1));
-                mbar_expect_tx(&bars->full[st], kTileBytes);
-                tma_load_1d(b_s + st * kTileBytes, bimg + c * (kTileBytes / 4), kTileBytes, &bars->full[st]);
+            mbar_expect_tx(&bars->a_full, C::ATILES * kTileBytes);
+            tma_load_1d(a_s, aimg + tile0 * (kTileBytes / 4), C::ATILES * kTileBytes, &bars->a_full);
+            for (int64_t it = 0; it < nchunks * NSUB; ++it) {
+                const int64_t c = it / NSUB;
+                const int sub = (int)(it % NSUB);
+                const int st = (int)(it % kStages);
+                const int kg0 = sub == 0 ? 0 : C::kSplit, kg1 = (NSUB == 1 || sub == 1) ? C::kKGroups : C::kSplit;
+                const uint32_t bytes = (uint32_t)((kg1 - kg0) * kLBO);
+                mbar_wait(&bars->empty[st], (uint32_t)(((it / kStages) & 1) ^ 1));
+                mbar_expect_tx(&bars->full[st], bytes);
+                tma_load_1d(b_s + st * C::kStageBytes, bimg + c * (kTileBytes / 4) + kg0 * (kLBO / 4), bytes, &bars->full[st]);
             }
         }
     } else if (warp == 9) {
@@ -211,27 +250,35 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
         if (lane == 0) {
             mbar_wait(&bars->a_full, 0);
             const uint32_t a_addr = smem_u32(a_s), b_addr = smem_u32(b_s);
-            // K-group pairs (A kg, B kg) of the 7 K=8 steps: hi.hi, hi.hi, lo.hi, lo.hi, hi.lo, hi.lo, ones.norm
-            const int akg[7] = {0, 2, 4, 6, 0, 2, 8};
-            const int bkg[7] = {0, 2, 0, 2, 4, 6, 8};
+            constexpr int kHiSteps = NSUB == 1 ? C::kSteps : 2 * (C::DP / 8);  // steps that read B sub-tile 0
             for (int64_t c = 0; c < nchunks; ++c) {
-                const int st = (int)(c % kStages), buf = (int)(c & 1);
+                const int buf = (int)(c & 1);
                 mbar_wait(&bars->tmem_empty[buf], (uint32_t)(((c >> 1) & 1) ^ 1));
-                mbar_wait(&bars->full[st], (uint32_t)((c / kStages) & 1));
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
-                for (int a = 0; a < 2; ++a) {
-                    const uint32_t d_tmem = tmem_base + (uint32_t)((buf * 2 + a) * 128);
+                for (int sub = 0; sub < NSUB; ++sub) {
+                    const int64_t it = c * NSUB + sub;
+                    const int st = (int)(it % kStages);
+                    mbar_wait(&bars->full[st], (uint32_t)((it / kStages) & 1));
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const int t0 = sub == 0 ? 0 : kHiSteps, t1 = (NSUB == 1 || sub == 1) ? C::kSteps : kHiSteps;
+                    const int kg0 = sub == 0 ? 0 : C::kSplit;
 #pragma unroll
-                    for (int k = 0; k < 7; ++k)
-                        umma_tf32(d_tmem, umma_desc(a_addr + a * kTileBytes + akg[k] * kLBO),
-                                  umma_desc(b_addr + st * kTileBytes + bkg[k] * kLBO), k > 0 ? 1u : 0u);
+                    for (int a = 0; a < C::ATILES; ++a) {
+                        const uint32_t d_tmem = tmem_base + (uint32_t)((buf * C::ATILES + a) * 128);
+#pragma unroll
+                        for (int t = t0; t < t1; ++t) {
+                            int akg, bkg;
+                            mma_step<C::DP>(t, akg, bkg);
+                            umma_tf32(d_tmem, umma_desc(a_addr + a * kTileBytes + akg * kLBO),
+                                      umma_desc(b_addr + st * C::kStageBytes + (bkg - kg0) * kLBO), t > 0 ? 1u : 0u);
+                        }
+                    }
+                    umma_commit(&bars->empty[st]);  // smem stage reusable once these MMAs have read it
                 }
-                umma_commit(&bars->empty[st]);        // smem stage reusable once these MMAs have read it
-                umma_commit(&bars->tmem_full[buf]);   // accumulators of this chunk complete
+                umma_commit(&bars->tmem_full[buf]);  // accumulators of this chunk complete
             }
         }
-    } else {
+    } else if (warp < 4 * C::ATILES) {
         // ===== epilogue: thread = query row =====
         const int a = warp >> 2;  // which A tile; warp%4 selects the TMEM lane quarter this warp may read
         const int row = a * 128 + (warp & 3) * 32 + lane;  // row inside the CTA
@@ -258,7 +305,7 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
             const int buf = (int)(c & 1);
             mbar_wait(&bars->tmem_full[buf], (uint32_t)((c >> 1) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((buf * 2 + a) * 128);
+            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((buf * C::ATILES + a) * 128);
             const int32_t c0 = (int32_t)(c * kTileRows);
 #pragma unroll 1
             for (int part = 0; part < 4; ++part) {
@@ -290,26 +337,46 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
     }
 }
 
-}  // namespace
-
-int64_t knn_tc_padded_candidates(int64_t M) { return align_up(M, kTileRows); }
-int64_t knn_tc_padded_queries(int64_t nq) { return align_up(nq, kRowsPerCta); }
-int64_t knn_tc_image_floats(int64_t rows_padded) { return rows_padded * kRowFloats; }
-
-int knn_filter_tc(const float* z, int64_t M, int d, int64_t q_lo, int64_t nq, float* bimg, float* aimg,
-                  unsigned int* max_nrm_bits, int32_t* cand_idx, float* cand_thr, cudaStream_t st) {
-    if (d > 16) {
-        geocb_set_error("knn_filter_tc supports d <= 16");
-        return GEOCB_ERR_UNSUPPORTED;
-    }
-    const int64_t Mp = knn_tc_padded_candidates(M), nqp = knn_tc_padded_queries(nq);
-    const int64_t threads = (Mp + nqp) * kKGroups;
-    knn_tc_prep_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(z, M, d, Mp, q_lo, nq, nqp, bimg, aimg,
+template <class C>
+int launch_tc(const float* z, const float* zq, int64_t M, int d, int64_t nq, float* bimg, float* aimg,
+              unsigned int* max_nrm_bits, int32_t* cand_idx, float* cand_thr, cudaStream_t st) {
+    const int64_t Mp = align_up(M, kTileRows), nqp = align_up(nq, C::kRowsPerCta);
+    const int64_t threads = (Mp + nqp) * C::kKGroups;
+    knn_tc_prep_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(z, zq, M, d, C::DP, Mp, nq, nqp, bimg, aimg,
                                                                            max_nrm_bits);
     KERNEL_CHECK();
-    const size_t smem = (size_t)(2 + kStages) * kTileBytes + (size_t)kL * kRowsPerCta * 8 + sizeof(TcBars) + 64;
-    CU_TRY(cudaFuncSetAttribute(knn_filter_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    knn_filter_tc_kernel<<<(unsigned)(nqp / kRowsPerCta), kThreads, smem, st>>>(aimg, bimg, Mp, nq, cand_idx, cand_thr);
+    const size_t smem = (size_t)C::ATILES * C::kTileBytes + (size_t)C::STAGES * C::kStageBytes +
+                        (size_t)kL * C::kRowsPerCta * 8 + sizeof(TcBars<C::STAGES>) + 64;
+    auto kern = knn_filter_tc_kernel<C>;
+    CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)(nqp / C::kRowsPerCta), kThreads, smem, st>>>(aimg, bimg, Mp, nq, cand_idx, cand_thr);
     KERNEL_CHECK();
     return 0;
+}
+
+typedef Cfg<16, 2, 4, 1> Cfg16;
+typedef Cfg<32, 2, 2, 1> Cfg32;
+typedef Cfg<64, 1, 3, 2> Cfg64;
+static_assert(2 * Cfg16::kTileBytes + 4 * Cfg16::kStageBytes + kL * 256 * 8 < 227 * 1024, "smem");
+static_assert(2 * Cfg32::kTileBytes + 2 * Cfg32::kStageBytes + kL * 256 * 8 < 227 * 1024, "smem");
+static_assert(1 * Cfg64::kTileBytes + 3 * Cfg64::kStageBytes + kL * 128 * 8 < 227 * 1024, "smem");
+
+}  // namespace
+
+int knn_tc_dp(int d) { return d <= 16 ? 16 : d <= 32 ? 32 : 64; }
+int64_t knn_tc_padded_candidates(int64_t M) { return align_up(M, kTileRows); }
+int64_t knn_tc_padded_queries(int64_t nq, int d) { return align_up(nq, d <= 32 ? 256 : 128); }
+int64_t knn_tc_image_floats(int64_t rows_padded, int d) { return rows_padded * (2 * knn_tc_dp(d) + 8); }
+
+int knn_filter_tc(const float* z, const float* zq, int64_t M, int d, int64_t nq, float* bimg, float* aimg,
+                  unsigned int* max_nrm_bits, int32_t* cand_idx, float* cand_thr, cudaStream_t st) {
+    if (d > 64) {
+        geocb_set_error("knn_filter_tc supports d <= 64");
+        return GEOCB_ERR_UNSUPPORTED;
+    }
+    switch (knn_tc_dp(d)) {
+        case 16: return launch_tc<Cfg16>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
+        case 32: return launch_tc<Cfg32>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
+        default: return launch_tc<Cfg64>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
+    }
 }

@@ -39,8 +39,10 @@ def h2d(arr: np.ndarray, dev) -> torch.Tensor:
     sb, db = src.view(torch.uint8).reshape(-1), out.view(torch.uint8).reshape(-1)
     key = torch.device(dev).index
     if key not in _stage_bufs:
-        _stage_bufs[key] = [torch.empty(_STAGE_CHUNK, dtype=torch.uint8).pin_memory() for _ in range(2)]
-    bufs, evs = _stage_bufs[key], [None, None]
+        # (buffers, events): the events outlive the call -- the next upload must not overwrite a staging buffer whose
+        # DMA from the previous upload is still in flight
+        _stage_bufs[key] = ([torch.empty(_STAGE_CHUNK, dtype=torch.uint8).pin_memory() for _ in range(2)], [None, None])
+    bufs, evs = _stage_bufs[key]
     for i, off in enumerate(range(0, sb.numel(), _STAGE_CHUNK)):
         m = min(_STAGE_CHUNK, sb.numel() - off)
         if evs[i & 1] is not None:
@@ -156,6 +158,21 @@ def knn_topk(z, kq, q_lo=0, q_hi=None, want_dist=True):
     dist = torch.empty((nq, kq), dtype=torch.float32, device=z.device) if want_dist else None
     nun = torch.zeros(1, dtype=torch.int32, device=z.device)
     check(lib.geocb_knn_topk(ptr(z), M, d, q_lo, q_hi, kq, ptr(idx), ptr(dist), ptr(nun), stream_ptr()), "knn_topk")
+    return idx, dist, nun
+
+
+def knn_query(queries, cand, kq=1, want_dist=True):
+    """kq nearest rows of cand[M,d] for every row of queries[nq,d] (exact fp64 order, ties -> lowest index):
+    (idx int32 [nq,kq], dist f32 | None, n_exact_rows)."""
+    lib = _lib.load()
+    assert queries.is_cuda and cand.is_cuda and queries.dtype == cand.dtype == torch.float32
+    assert queries.is_contiguous() and cand.is_contiguous() and queries.shape[1] == cand.shape[1]
+    nq, d = queries.shape
+    idx = torch.empty((nq, kq), dtype=torch.int32, device=queries.device)
+    dist = torch.empty((nq, kq), dtype=torch.float32, device=queries.device) if want_dist else None
+    nun = torch.zeros(1, dtype=torch.int32, device=queries.device)
+    check(lib.geocb_knn_query(ptr(queries), nq, ptr(cand), cand.shape[0], d, kq, ptr(idx), ptr(dist), ptr(nun),
+                              stream_ptr()), "knn_query")
     return idx, dist, nun
 
 
