@@ -99,9 +99,12 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--skip-c1", action="store_true")
     ap.add_argument("--c3", action="store_true", help="only (re)generate c3_digest.npz")
+    ap.add_argument("--c4", action="store_true", help="only (re)generate c4_legacy.npz (legacy YAML drivers)")
     a = ap.parse_args()
     if a.c3:
         return make_c3()
+    if a.c4:
+        return make_c4()
 
     # ---------------- s1: full stage-boundary arrays ----------------
     z4 = torch.randn(125, 16, 4, 4, generator=torch.Generator().manual_seed(42))
@@ -200,6 +203,72 @@ def make_c3():
         ref_seconds=np.array([r["tm"]["knn"], r["tm"]["edge_len"], r["tm"]["kmedoids"], total]),
     )
     print("c3:", "E", len(r["L"]), "nnz", Wl.nnz, "qe", r["qe"], "med[:5]", r["med"][:5], r["tm"], "total", total)
+
+
+C4_VAE_CFG = dict(in_channels=3, output_image_size=32, latent_dim=32, enc_channels=[16, 32, 64],
+                  dec_channels=[64, 32, 16], recon_loss="mse", norm_type="batch", mse_use_sigmoid=False,
+                  free_bits_default=0.25, capacity_max_default=25.0, capacity_anneal_steps_default=100000,
+                  capacity_mode_default="abs")
+
+
+def c4_inputs(tmp):
+    """Flat latents + a random-init vanilla VAE checkpoint, written where the legacy drivers read them."""
+    from src.models.vae import VAE
+    z = torch.randn(3000, 32, generator=torch.Generator().manual_seed(42))
+    torch.save(z, tmp / "z.pt")
+    torch.manual_seed(0)
+    vae = VAE(**C4_VAE_CFG)
+    torch.save({"model_state_dict": vae.state_dict(), "epoch": 0}, tmp / "best.pt")
+    return z, vae
+
+
+def c4_configs(tmp):
+    """Shape of configs/cifar10/vanilla/{geodesic,euclidean}/codebook.yaml at a CPU-runnable size; `riemannian.mode: full`
+    because the shipped `subset` mode samples with NumPy's unseeded global RNG (not reproducible)."""
+    riem = {"data": {"dataset": "cifar10", "latents_path": str(tmp / "z.pt")}, "model": dict(C4_VAE_CFG),
+            "checkpoint_path": str(tmp / "best.pt"),
+            "graph": {"k": 10, "metric": "euclidean", "sym": "union", "mode": "distance"},
+            "riemannian": {"mode": "full", "max_edges": 5000, "batch_size": 512},
+            "quantize": {"K": 64, "init": "kpp", "seed": 42}, "out": {"dir": str(tmp / "out_riem")}}
+    euc = {"data": {"dataset": "cifar10", "latents_path": str(tmp / "z.pt")},
+           "graph": {"k": 10, "metric": "euclidean", "sym": "union", "mode": "connectivity"},
+           "quantize": {"K": 64, "init": "kpp", "seed": 42}, "out": {"dir": str(tmp / "out_euc")}}
+    return riem, euc
+
+
+def make_c4():
+    """Legacy YAML drivers (BASELINE configs[3] shape): src/training/build_riemannian_codebook_legacy.py:169-291 with
+    eval-mode BatchNorm and both edge directions re-weighted, and src/training/build_codebook_legacy.py:27-99 on a
+    unit-weight (hop count) graph."""
+    import tempfile
+    from src.training.build_riemannian_codebook_legacy import build_and_save as riem_build
+    from src.training.build_codebook_legacy import build_and_save as euc_build
+    with tempfile.TemporaryDirectory() as td:
+        tmp = Path(td)
+        c4_inputs(tmp)
+        riem, euc = c4_configs(tmp)
+        with contextlib.redirect_stdout(io.StringIO()):
+            riem_build(riem)
+            euc_build(euc)
+        Wr = sparse.load_npz(tmp / "out_riem" / "knn_graph_riemannian.npz").tocsr()
+        We = sparse.load_npz(tmp / "out_riem" / "knn_graph_euclidean.npz").tocsr()
+        Wk = sparse.load_npz(tmp / "out_euc" / "knn_graph.npz").tocsr()
+        for W in (Wr, We, Wk):
+            W.sort_indices()
+        cb_r = torch.load(tmp / "out_riem" / "codebook.pt", weights_only=False)
+        cb_e = torch.load(tmp / "out_euc" / "codebook.pt", weights_only=False)
+        codes_r, codes_e = np.load(tmp / "out_riem" / "codes.npy"), np.load(tmp / "out_euc" / "codes.npy")
+        np.savez_compressed(
+            HERE / "c4_legacy.npz",
+            riem_indptr=Wr.indptr, riem_indices=Wr.indices, riem_data=Wr.data, euc_data_sha=np.array(sha(We.data)),
+            riem_medoids=cb_r["medoid_indices"], riem_codes=codes_r, riem_method=np.array(cb_r["method"]),
+            riem_z_medoid_sha=np.array(sha(cb_r["z_medoid"].numpy())),
+            knn_indptr=Wk.indptr, knn_indices=Wk.indices, euc_medoids=cb_e["medoid_indices"], euc_codes=codes_e,
+            codes_dtypes=np.array([str(codes_r.dtype), str(codes_e.dtype)]),
+            graph_stats_keys=np.array(sorted(cb_r["graph_stats"])), n_components=np.int64(cb_r["graph_stats"]["n_components"]),
+        )
+        print("c4: riem nnz", Wr.nnz, "medoids[:5]", cb_r["medoid_indices"][:5], "codes", codes_r.shape, codes_r.dtype,
+              "| euclid nnz", Wk.nnz, "medoids[:5]", cb_e["medoid_indices"][:5], codes_e.dtype)
 
 
 if __name__ == "__main__":

@@ -24,6 +24,26 @@ _STAGE_CHUNK = 32 << 20
 _stage_bufs = {}
 
 
+_copy_pool = None
+
+
+def _host_copy(dst: torch.Tensor, src: torch.Tensor, parts=4):
+    """dst.copy_(src) for byte tensors on the host, split over a few Python threads (Tensor.copy_ releases the GIL):
+    under torchrun OMP_NUM_THREADS is 1, and one core moves only ~8 GB/s into pinned memory."""
+    global _copy_pool
+    n = dst.numel()
+    if n < (4 << 20):
+        dst.copy_(src)
+        return
+    if _copy_pool is None:
+        from concurrent.futures import ThreadPoolExecutor
+        _copy_pool = ThreadPoolExecutor(max_workers=parts)
+    step = -(-n // parts)
+    futs = [_copy_pool.submit(dst[o:o + step].copy_, src[o:o + step]) for o in range(0, n, step)]
+    for f in futs:
+        f.result()
+
+
 def h2d(arr: np.ndarray, dev) -> torch.Tensor:
     """Pageable NumPy array -> device tensor through two pinned staging buffers: the (multi-threaded) host copy of
     chunk i+1 into pinned memory overlaps the DMA of chunk i, so large arrays move at PCIe speed instead of the
@@ -47,7 +67,7 @@ def h2d(arr: np.ndarray, dev) -> torch.Tensor:
         m = min(_STAGE_CHUNK, sb.numel() - off)
         if evs[i & 1] is not None:
             evs[i & 1].synchronize()  # the DMA out of this staging buffer has finished
-        bufs[i & 1][:m].copy_(sb[off:off + m])
+        _host_copy(bufs[i & 1][:m], sb[off:off + m])
         db[off:off + m].copy_(bufs[i & 1][:m], non_blocking=True)
         evs[i & 1] = torch.cuda.Event()
         evs[i & 1].record()

@@ -178,6 +178,51 @@ def _gn_pair(m, x, t):
     return xh, th
 
 
+def _flat_decoder_layers(decoder):
+    """Layer list of the reference's flat-latent decoder (src/models/vae.py:53-85: fc -> view(C,4,4) -> deconv1 ->
+    deconv2 -> output_layer), or None for anything else."""
+    need = ("fc", "deconv1", "deconv2", "output_layer")
+    if not all(hasattr(decoder, a) for a in need) or [n for n, _ in decoder.named_children()] != list(need):
+        return None
+    if not isinstance(decoder.fc, nn.Linear) or not isinstance(decoder.output_layer, nn.ConvTranspose2d):
+        return None
+    out = [decoder.fc, ("view", (-1, 4, 4))]
+    for blk in (decoder.deconv1, decoder.deconv2):
+        for m in blk:
+            if not isinstance(m, (nn.ConvTranspose2d, nn.Conv2d, nn.BatchNorm2d, nn.GroupNorm, nn.ReLU, nn.Identity)):
+                return None
+            out.append(m)
+    out.append(decoder.output_layer)
+    return out
+
+
+def _forward_mode_modules(layers, z, dz, groups):
+    """Tangent of sigmoid(decoder(z)) along dz through the decoder's own layers in explicit forward mode: primal and
+    tangent share every linear / convolution call (stacked along the batch), norms and ReLU propagate the tangent in
+    closed form.  Used for the flat-latent decoder, whose dense unrolling would be ~10x the convolution flops."""
+    n = z.shape[0]
+    x, t = z, dz
+    for m in layers:
+        if isinstance(m, tuple):  # ("view", (C, H, W))
+            x, t = x.view(n, *m[1]), t.view(n, *m[1])
+        elif isinstance(m, nn.Linear):
+            y = torch.cat([x, t], 0) @ m.weight.t()
+            x, t = y[:n], y[n:]
+            if m.bias is not None:
+                x = x + m.bias
+        elif isinstance(m, (nn.Conv2d, nn.ConvTranspose2d)):
+            x, t = _conv_pair(m, x, t)
+        elif isinstance(m, nn.BatchNorm2d):
+            x, t = _bn_pair(m, x, t, groups)
+        elif isinstance(m, nn.GroupNorm):
+            x, t = _gn_pair(m, x, t)
+        elif isinstance(m, nn.ReLU):
+            t = t * (x > 0)
+            x = torch.relu(x)
+    s = torch.sigmoid(x)  # always applied (:29)
+    return (s * (1 - s) * t).reshape(n, -1)
+
+
 def _unique_taps(m):
     """True when every (input position, output position) pair is linked by at most one kernel tap, i.e. the dense
     matrix entries are single weights (always the case for dilation 1)."""
@@ -333,15 +378,18 @@ def edge_lengths_device(decoder, z_flat, ei, ej, batch_size=512, pos_ij=None, po
     assert e_lo % batch_size == 0
     dev = z_flat.device
     out = torch.empty(max(e_hi - e_lo, 0), dtype=torch.float32, device=dev)
+    flat_layers = _flat_decoder_layers(decoder) if _is_flat_decoder(decoder) else None
     layers = None if _is_flat_decoder(decoder) else _flatten_layers(decoder)
     if layers is not None:
         with _strict_fp32():
             layers = _unrolled_ops(layers, z_flat.shape[1])
+    if flat_layers is not None:
+        groups_per_call = min(groups_per_call, 8)  # full-resolution feature maps: bound the activation memory
     with _strict_fp32():
         lo = e_lo
         while lo < e_hi:
             full = (e_hi - lo) // batch_size
-            if layers is not None and full >= 1:
+            if (layers is not None or flat_layers is not None) and full >= 1:
                 g = min(full, groups_per_call)
                 hi = lo + g * batch_size
             else:
@@ -352,6 +400,9 @@ def edge_lengths_device(decoder, z_flat, ei, ej, batch_size=512, pos_ij=None, po
             if layers is not None:
                 # start- and end-point JVPs are separate decoder calls in the reference => separate BN groups
                 j = _forward_mode(layers, torch.cat([a, b], 0), torch.cat([d, d], 0), 2 * g)
+                ja, jb = j[: hi - lo].contiguous(), j[hi - lo:].contiguous()
+            elif flat_layers is not None:
+                j = _forward_mode_modules(flat_layers, torch.cat([a, b], 0), torch.cat([d, d], 0), 2 * g)
                 ja, jb = j[: hi - lo].contiguous(), j[hi - lo:].contiguous()
             else:
                 with torch.enable_grad():
