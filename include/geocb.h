@@ -97,6 +97,16 @@ int geocb_edge_len_scatter(const float* ja, const float* jb, int64_t E, int P, i
 int geocb_bn_relu_jvp(float* x, float* t, int64_t rows, int C, int HW, int rows_per_group, const float* pre_bias,
                       const float* weight, const float* bias, float eps, int relu, void* stream);
 
+/* fp32-grade GEMM on the tcgen05 tensor cores for the decoder-JVP layers (csrc/jvp_gemm.cu; replaces the cuBLAS SGEMM
+ * behind the 512 -> 1024 layer of the unrolled decoder): C[M,N] = A[M,K] @ W[K,N], every operand split into tf32
+ * hi + lo parts, three MMAs per K-step (hi.hi + lo.hi + hi.lo), fp32 accumulation in TMEM.
+ * geocb_gemm3x_prep_weights writes the weight image bimg[2*K*N] once per matrix; geocb_gemm3x needs a scratch image
+ * aimg[2*M*K] and shapes with M % 256 == 0, K % 16 == 0, N % 256 == 0 (geocb_gemm3x_supported), else
+ * GEOCB_ERR_UNSUPPORTED and the caller keeps the library GEMM. */
+int geocb_gemm3x_supported(int64_t M, int K, int N);
+int geocb_gemm3x_prep_weights(const float* W, int K, int N, float* bimg, void* stream);
+int geocb_gemm3x(const float* A, int64_t M, int K, int N, const float* bimg, float* aimg, float* C, void* stream);
+
 /* --------------------------------------------- connected components ------
  * replaces scipy.sparse.csgraph.connected_components (knn_graph_optimized.py:175).
  * labels[n] = smallest vertex id of the component (undirected: the CSR must be

@@ -250,6 +250,30 @@ def bn_relu_jvp(x, t, C_, HW, rows_per_group, pre_bias, weight, bias, eps, relu)
     return True
 
 
+_gemm3x_weights = {}
+
+
+def gemm3x(a: torch.Tensor, w: torch.Tensor):
+    """a[M,K] @ w[K,N] through the tcgen05 3xTF32 GEMM (fp32-grade), or None when the shape is unsupported.
+    The weight image is built once per weight tensor; the activation image buffer is cached per device."""
+    lib = _lib.load()
+    M, K = a.shape
+    N = w.shape[1]
+    if not (a.is_contiguous() and w.is_contiguous() and a.dtype == w.dtype == torch.float32
+            and lib.geocb_gemm3x_supported(M, K, N)):
+        return None
+    key = (w.data_ptr(), K, N)
+    if key not in _gemm3x_weights:
+        bimg = torch.empty(2 * K * N, dtype=torch.float32, device=w.device)
+        check(lib.geocb_gemm3x_prep_weights(ptr(w), K, N, ptr(bimg), stream_ptr()), "gemm3x_prep_weights")
+        _gemm3x_weights[key] = (bimg, w)  # keep w alive so the pointer stays unique
+    bimg = _gemm3x_weights[key][0]
+    aimg = _workspace("gemm3x_a", 2 * M * K * 4, a.device)
+    c = torch.empty((M, N), dtype=torch.float32, device=a.device)
+    check(lib.geocb_gemm3x(ptr(a), M, K, N, ptr(bimg), ptr(aimg), ptr(c), stream_ptr()), "gemm3x")
+    return c
+
+
 # ------------------------------------------------------------ components / LCC
 def component_labels(g: DeviceCSR):
     lib = _lib.load()

@@ -63,40 +63,16 @@ def _strict_fp32():
         torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = a, b
 
 
-# ------------------------------------------------------------ experimental: 3xTF32 GEMM (opt-in, off by default)
-def _tf32_round(x: torch.Tensor) -> torch.Tensor:
-    """Nearest value with a 10-bit mantissa (what a tensor core reads of an fp32 operand), ties away from zero."""
-    return ((x.contiguous().view(torch.int32) + 0x1000) & -8192).view(torch.float32)
-
-
-_W_SPLIT = {}
-
-
-def _mm_split3(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
-    """x @ w as three TF32 tensor-core GEMMs on hi/lo splits (x_hi w_hi + x_lo w_hi + x_hi w_lo, fp32 accumulate): the
-    dropped x_lo w_lo term and the truncation of the lo parts are ~2^-22 relative, i.e. below fp32 accumulation noise.
-    EXPERIMENTAL (env GEOCB_JVP_3XTF32=1): ~2x faster than cuBLAS SGEMM for the 512->1024 layer but not yet
-    parity-qualified against the ReLU-kink tolerance of DESIGN.md section 2, so the default path stays true fp32."""
-    key = (w.data_ptr(), w.shape)
-    if key not in _W_SPLIT:
-        wh = _tf32_round(w)
-        _W_SPLIT[key] = (wh, (w - wh).contiguous(), w)  # keep w alive so the pointer stays unique
-    wh, wl, _ = _W_SPLIT[key]
-    xh = _tf32_round(x)
-    xl = x - xh
-    prev = torch.backends.cuda.matmul.allow_tf32
-    torch.backends.cuda.matmul.allow_tf32 = True
-    try:
-        y = xh @ wh
-        y.addmm_(xl, wh)
-        y.addmm_(xh, wl)
-    finally:
-        torch.backends.cuda.matmul.allow_tf32 = prev
-    return y
-
-
-def _use_split3(k_dim: int) -> bool:
-    return os.environ.get("GEOCB_JVP_3XTF32", "0") == "1" and k_dim >= 256
+# ------------------------------------------------------------ tensor-core GEMM for the wide decoder layer
+def _lin(xin: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    """xin @ w.  Layers with K >= 256 go through the hand-written tcgen05 3xTF32 GEMM (csrc/jvp_gemm.cu: fp32-grade,
+    ~3x the cuBLAS SIMT SGEMM); GEOCB_JVP_GEMM=cublas keeps the library SGEMM.  Unsupported shapes (a short last
+    batch) use the library GEMM."""
+    if w.shape[0] >= 256 and os.environ.get("GEOCB_JVP_GEMM", "tc") == "tc":
+        y = dg.gemm3x(xin.contiguous(), w)
+        if y is not None:
+            return y
+    return xin @ w
 
 
 # ------------------------------------------------------------ explicit forward mode
@@ -322,7 +298,7 @@ def _forward_mode(ops, z, dz, groups):
         op = ops[i]
         if op[0] == "lin":
             xin = stacked if stacked is not None else torch.cat([x, t], 0)  # primal and tangent share one GEMM
-            y = _mm_split3(xin, op[1]) if _use_split3(op[1].shape[0]) else xin @ op[1]
+            y = _lin(xin, op[1])
             x, t = y[:n], y[n:]
             stacked = y
             pending_bias = op[2]
