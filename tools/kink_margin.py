@@ -30,7 +30,9 @@ import numpy as np
 import torch
 import torch.nn as nn
 
-EPS = 2e-6          # |pre-activation| below which a float32 ReLU mask is undecidable (activations are O(1); largest margin seen on a flipped edge: 5.4e-7)
+EPS = 1e-5          # |pre-activation| below which a ReLU mask is treated as undecidable (activations are O(1)).  Largest margin seen
+                    # on a flipped edge: 5.4e-7 with fp32 SIMT GEMMs (reference fp32 vs fp64, and GEOCB_JVP_GEMM=cublas), 4.2e-6 with the
+                    # tcgen05 3xTF32 GEMM, whose error is 1.3-1.9e-6 x sum|a||w| against 3e-7 (tests/test_gpu_jvp_gemm.py)
 COUPLED_TOL = 1e-4  # bound on the deviation a flipped unit elsewhere in the BatchNorm batch can cause
 
 
@@ -89,7 +91,7 @@ def check_edge_lengths(got, ref, decoder, z_start, z_end, batch_size, positions=
     report = {"edges": int(len(ref)), "beyond_tol": int(len(bad)), "max_rel": float(rel.max()) if len(rel) else 0.0,
               "median_rel": float(np.median(rel)) if len(rel) else 0.0, "own_kink": 0, "batch_kink": 0}
     assert report["median_rel"] <= 1e-6, report
-    assert len(bad) <= max(8, 0.005 * len(ref)), f"{len(bad)} of {len(ref)} edges beyond {tol}: not a kink effect"
+    assert len(bad) <= max(8, 0.002 * len(ref)), f"{len(bad)} of {len(ref)} edges beyond {tol}: not a kink effect"
     if len(bad):
         marg = relu_margins(decoder, z_start, z_end, batch_size, pos[bad])
         for i in bad:

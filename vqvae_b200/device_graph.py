@@ -326,8 +326,35 @@ def _workspace(tag, nbytes, device, zero=False):
 
 
 def default_slots(n):
-    """Concurrent sources per launch (measured on B200 at n=2.94M: throughput rises up to 16; 20 B/vertex/slot)."""
-    return 16
+    """Concurrent sources per launch.  Measured on B200 at n=2.94M: throughput rises up to 16 slots and is flat to 32
+    (profiles/r1_sssp_variant_sweep_delta4.txt); every slot costs 20.4 B per vertex of workspace plus 4 B per vertex of
+    output row, so very large graphs are capped by what is free on the device (a quarter of it at most)."""
+    slots = 16
+    try:
+        free, _ = torch.cuda.mem_get_info()
+        slots = int(max(1, min(slots, (free // 4) // max(1, 25 * n))))
+    except Exception:
+        pass
+    return slots
+
+
+def _delta_for(g, mean_w, unweighted):
+    """Bucket width = scale x mean edge weight.  Any width gives the same bits; 4x is best on the C2 geodesic graph
+    (1x: 110, 2x: 117, 4x: 120, 6x: 117 G edge-relax/s), but on graphs with a wide weight spread it re-relaxes too much
+    (hash-weight proxy: 1.85 relaxations per edge at 4x against 1.13 at 1x).  The kernel returns its relaxation count,
+    so the scale adapts per graph: halved while a call spends more than 1.35 relaxations per edge."""
+    env = os.environ.get("GEOCB_SSSP_DELTA_SCALE")
+    scale = float(env) if env else g._adj.get(("delta_scale", bool(unweighted)), 4.0)
+    return (mean_w if mean_w > 0 else 1.0) * scale
+
+
+def _delta_feedback(g, unweighted, relax, S):
+    if os.environ.get("GEOCB_SSSP_DELTA_SCALE") or S <= 0 or g.nnz <= 0:
+        return
+    key = ("delta_scale", bool(unweighted))
+    scale = g._adj.get(key, 4.0)
+    if relax / (S * float(g.nnz)) > 1.35 and scale > 0.5:
+        g._adj[key] = scale / 2
 
 
 def vm_default_blocks(n):
@@ -386,10 +413,9 @@ def sssp_multi(g: DeviceCSR, sources, unweighted=False, want_pred=False, delta=N
     S = int(src.numel())
     if _pick_kernel(kernel, S, want_pred) == "vm":
         return sssp_multi_vm(g, sources, unweighted=unweighted, delta=delta, out=out, stats=stats)
-    if delta is None:
-        # bucket width = 4 x mean edge weight: measured best on the 2.94M-vertex geodesic graph (1x: 110, 2x: 117,
-        # 4x: 120, 6x: 117, 10x: 117 G edge-relax/s; relaxations per edge 1.03 -> 1.06, rounds per source batch 19 -> 13)
-        delta = (mean_w if mean_w > 0 else 1.0) * float(os.environ.get("GEOCB_SSSP_DELTA_SCALE", "4"))
+    auto_delta = delta is None
+    if auto_delta:
+        delta = _delta_for(g, mean_w, unweighted)
     slots = default_slots(g.n) if slots is None else slots
     slots = max(1, min(slots, S, 32))
     nbytes = lib.geocb_sssp_workspace_bytes(g.n, slots)
@@ -402,6 +428,8 @@ def sssp_multi(g: DeviceCSR, sources, unweighted=False, want_pred=False, delta=N
         in_ptr, in_adj, _ = g_in.adjacency(unweighted)
     check(lib.geocb_sssp_multi(ptr(row_ptr), ptr(adj), g.n, ptr(src), S, float(delta), slots, ptr(ws), ws.numel(),
                                ptr(D), ptr(P), ptr(in_ptr), ptr(in_adj), st, stream_ptr()), "sssp_multi")
+    if auto_delta:
+        _delta_feedback(g, unweighted, st[0], S)
     res = (D, P) if want_pred else D
     if stats:
         return res, dict(relaxations=st[0], rounds=st[1], scans=st[2], improvements=st[3], slots=slots, delta=delta,

@@ -31,7 +31,7 @@ def _cosine_rows(z_dev: torch.Tensor) -> torch.Tensor:
 
 
 def knn_graph_device(z_dev: torch.Tensor, k: int, mode: str = "distance", sym: str = "mutual",
-                     metric: str = "euclidean"):
+                     metric: str = "euclidean", after_launch=None):
     """Device-side body shared by every public builder.
 
     z_dev: (N,D) float32 CUDA tensor, N >= 2, 1 <= k <= N-1.
@@ -54,6 +54,8 @@ def knn_graph_device(z_dev: torch.Tensor, k: int, mode: str = "distance", sym: s
             dist[sl] = (1.0 - dots).clamp_(0.0, 2.0).float()
     elif metric == "euclidean":
         idx, dist, _ = dg.knn_topk(z_dev, k + 1)  # k+1 query incl. self (:39-42)
+        if after_launch is not None:
+            after_launch()  # host-side work the caller wants overlapped with the (asynchronous) search
     else:
         raise ValueError(f"metric '{metric}' not supported. Use 'euclidean' or 'cosine'.")  # :99
     me = torch.arange(N, device=z_dev.device, dtype=torch.int32)

@@ -340,6 +340,38 @@ def _forward_mode(ops, z, dz, groups):
     return s * (1 - s) * t
 
 
+def decoder_plan(decoder, latent_dim):
+    """(dense-operator list | None, flat-decoder layer list | None) for `decoder`, cached on the module and rebuilt
+    when a parameter or the train/eval mode changes.  Building it costs tens of milliseconds of host work (and the
+    first GEMM creates the cuBLAS handle), which the pipeline overlaps with the kNN kernel (warm_up_decoder)."""
+    key = (latent_dim, tuple((p.data_ptr(), p._version) for p in decoder.parameters()),
+           tuple(m.training for m in decoder.modules()))
+    cached = getattr(decoder, "_geocb_plan", None)
+    if cached is not None and cached[0] == key:
+        return cached[1], cached[2]
+    flat_layers = _flat_decoder_layers(decoder) if _is_flat_decoder(decoder) else None
+    layers = None if _is_flat_decoder(decoder) else _flatten_layers(decoder)
+    if layers is not None:
+        with _strict_fp32():
+            layers = _unrolled_ops(layers, latent_dim)
+    object.__setattr__(decoder, "_geocb_plan", (key, layers, flat_layers))
+    return layers, flat_layers
+
+
+@torch.no_grad()
+def warm_up_decoder(decoder, latent_dim, batch_size=512):
+    """Build the plan and push one tiny batch through it (current stream): creates library handles, weight images and
+    the allocator's first blocks off the critical path.  Results are discarded; BatchNorm buffers are not touched
+    (the explicit forward mode never calls the modules)."""
+    layers, flat = decoder_plan(decoder, latent_dim)
+    if layers is None:
+        return
+    dev = next(decoder.parameters()).device
+    z = torch.zeros((2 * batch_size, latent_dim), device=dev)
+    with _strict_fp32():
+        _forward_mode(layers, z, z, 2)
+
+
 @torch.no_grad()
 def edge_lengths_device(decoder, z_flat, ei, ej, batch_size=512, pos_ij=None, pos_ji=None, csr_data=None,
                         e_lo=0, e_hi=None, groups_per_call=64):
@@ -354,11 +386,7 @@ def edge_lengths_device(decoder, z_flat, ei, ej, batch_size=512, pos_ij=None, po
     assert e_lo % batch_size == 0
     dev = z_flat.device
     out = torch.empty(max(e_hi - e_lo, 0), dtype=torch.float32, device=dev)
-    flat_layers = _flat_decoder_layers(decoder) if _is_flat_decoder(decoder) else None
-    layers = None if _is_flat_decoder(decoder) else _flatten_layers(decoder)
-    if layers is not None:
-        with _strict_fp32():
-            layers = _unrolled_ops(layers, z_flat.shape[1])
+    layers, flat_layers = decoder_plan(decoder, z_flat.shape[1])
     if flat_layers is not None:
         groups_per_call = min(groups_per_call, 8)  # full-resolution feature maps: bound the activation memory
     with _strict_fp32():

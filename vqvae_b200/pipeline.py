@@ -19,7 +19,7 @@ from . import _lib
 from . import device_graph as dg
 from .sharding import shard_range, all_gather_rows  # noqa: F401  (re-exported)
 from .geo.knn_graph_optimized import knn_graph_device
-from .geo.riemannian_metric import edge_lengths_device
+from .geo.riemannian_metric import edge_lengths_device, warm_up_decoder
 from .geo.kmeans_optimized import fit_kmedoids_optimized
 
 
@@ -84,11 +84,21 @@ def build_codebook_device(z4: torch.Tensor, decoder, k=20, sym="union", K=512, i
     k_eff = max(1, min(k, M - 1))
     # ---- kNN + symmetrise (knn_graph_optimized.py) ----
     tm("knn")
+    side = torch.cuda.Stream(device=dev)
+
+    def overlap_decoder_setup():
+        # the kNN kernel is in flight (nothing above synchronises): unroll the decoder, build its weight images and
+        # create the GEMM handles on a side stream meanwhile instead of in front of the edge-length stage
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            warm_up_decoder(decoder, C, batch_size)
+
     if world == 1:
-        g_euc, _, _ = knn_graph_device(z_flat, k_eff, "connectivity", sym)
+        g_euc, _, _ = knn_graph_device(z_flat, k_eff, "connectivity", sym, after_launch=overlap_decoder_setup)
     else:
         lo, hi = shard_range(M, rank, world)
         idx, dst, _ = dg.knn_topk(z_flat, k_eff + 1, lo, hi)
+        overlap_decoder_setup()
         tm("knn_gather")
         idx = all_gather_rows(idx, M, world, rank, group, dist)
         dst = all_gather_rows(dst, M, world, rank, group, dist)
@@ -109,6 +119,7 @@ def build_codebook_device(z4: torch.Tensor, decoder, k=20, sym="union", K=512, i
         print(f"Re-weighting {E} edges using Riemannian metric...")
     # ---- Riemannian lengths, scattered into both CSR directions (:51-54) ----
     tm("edge_len")
+    torch.cuda.current_stream(dev).wait_stream(side)
     g_geo = dg.DeviceCSR(g_euc.indptr, g_euc.indices, torch.zeros_like(g_euc.data), M)
     if world == 1:
         L = edge_lengths_device(decoder, z_flat, ei, ej, batch_size, pos_ij, pos_ji, g_geo.data)
