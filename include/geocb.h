@@ -103,6 +103,12 @@ int geocb_bn_relu_jvp(float* x, float* t, int64_t rows, int C, int HW, int rows_
  * geocb_gemm3x_prep_weights writes the weight image bimg[2*K*N] once per matrix; geocb_gemm3x needs a scratch image
  * aimg[2*M*K] and shapes with M % 256 == 0, K % 16 == 0, N % 256 == 0 (geocb_gemm3x_supported), else
  * GEOCB_ERR_UNSUPPORTED and the caller keeps the library GEMM. */
+/* geocb_bn_relu_jvp_to_image: same arithmetic as geocb_bn_relu_jvp, but the result is written as the tf32 hi | lo
+ * operand image of the GEMM that follows (primal rows at [0, rows), tangent rows at [img_row_t, ...) of its A matrix;
+ * rows and img_row_t multiples of 128, K = C*HW) instead of in place; geocb_gemm3x then takes A = NULL. */
+int geocb_bn_relu_jvp_to_image(const float* x, const float* t, int64_t rows, int C, int HW, int rows_per_group,
+                               const float* pre_bias, const float* weight, const float* bias, float eps, int relu,
+                               float* aimg, int64_t img_row_t, void* stream);
 int geocb_gemm3x_supported(int64_t M, int K, int N);
 int geocb_gemm3x_prep_weights(const float* W, int K, int N, float* bimg, void* stream);
 int geocb_gemm3x(const float* A, int64_t M, int K, int N, const float* bimg, float* aimg, float* C, void* stream);

@@ -40,7 +40,8 @@ template <int RPT, int CPB>
 __global__ void __launch_bounds__(kBnThreads) bn_relu_jvp_kernel(float* __restrict__ x, float* __restrict__ t, int R,
                                                                  int ld, const float* __restrict__ pre_bias,
                                                                  const float* __restrict__ weight,
-                                                                 const float* __restrict__ bias, float eps, int relu) {
+                                                                 const float* __restrict__ bias, float eps, int relu,
+                                                                 float* __restrict__ img, int64_t img_row_t) {
     constexpr int HW = 16 / CPB;
     __shared__ float s_red[(kBnThreads / 32) * 2 * CPB];
     const int col0 = blockIdx.x * 16;
@@ -146,6 +147,32 @@ __global__ void __launch_bounds__(kBnThreads) bn_relu_jvp_kernel(float* __restri
                 ot[c * HW + h] = ty;
             }
         }
+        if (img) {
+            // The next layer is the tcgen05 3xTF32 GEMM (jvp_gemm.cu): write its operand image directly -- tf32 hi | lo
+            // halves of this 16-float slab (= one K-chunk) in the UMMA canonical layout -- instead of the row-major
+            // activations.  Primal rows sit at [0, rows), tangent rows at [img_row_t, img_row_t + rows) of the GEMM's A.
+            const int nchunks = ld / 16;
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const int64_t arow = (half ? img_row_t : 0) + row0 + r;
+                float* base = img + (((arow >> 7) * nchunks + blockIdx.x) * 2) * 2048 + (arow & 127) * 4;
+                const float* v = half ? ot : ox;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    float hi[4], lo[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        uint32_t hb;
+                        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hb) : "f"(v[4 * q + i]));
+                        hi[i] = __uint_as_float(hb);
+                        lo[i] = v[4 * q + i] - hi[i];
+                    }
+                    *(float4*)(base + q * 512) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+                    *(float4*)(base + q * 512 + 2048) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+                }
+            }
+            continue;
+        }
         float4* px = (float4*)(x + (row0 + r) * ld + col0);
         float4* pt = (float4*)(t + (row0 + r) * ld + col0);
 #pragma unroll
@@ -158,13 +185,13 @@ __global__ void __launch_bounds__(kBnThreads) bn_relu_jvp_kernel(float* __restri
 
 template <int RPT>
 int launch_bn(int cpb, dim3 grid, cudaStream_t st, float* x, float* t, int R, int ld, const float* pre_bias,
-              const float* weight, const float* bias, float eps, int relu) {
+              const float* weight, const float* bias, float eps, int relu, float* img, int64_t img_row_t) {
     switch (cpb) {
-        case 1: bn_relu_jvp_kernel<RPT, 1><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu); break;
-        case 2: bn_relu_jvp_kernel<RPT, 2><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu); break;
-        case 4: bn_relu_jvp_kernel<RPT, 4><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu); break;
-        case 8: bn_relu_jvp_kernel<RPT, 8><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu); break;
-        case 16: bn_relu_jvp_kernel<RPT, 16><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu); break;
+        case 1: bn_relu_jvp_kernel<RPT, 1><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t); break;
+        case 2: bn_relu_jvp_kernel<RPT, 2><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t); break;
+        case 4: bn_relu_jvp_kernel<RPT, 4><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t); break;
+        case 8: bn_relu_jvp_kernel<RPT, 8><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t); break;
+        case 16: bn_relu_jvp_kernel<RPT, 16><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t); break;
         default: return GEOCB_ERR_UNSUPPORTED;
     }
     KERNEL_CHECK();
@@ -172,9 +199,8 @@ int launch_bn(int cpb, dim3 grid, cudaStream_t st, float* x, float* t, int R, in
 }
 }  // namespace
 
-GEOCB_API int geocb_bn_relu_jvp(float* x, float* t, int64_t rows, int C, int HW, int rows_per_group,
-                                const float* pre_bias, const float* weight, const float* bias, float eps, int relu,
-                                void* stream) {
+static int bn_impl(float* x, float* t, int64_t rows, int C, int HW, int rows_per_group, const float* pre_bias,
+                   const float* weight, const float* bias, float eps, int relu, float* img, int64_t img_row_t, void* stream) {
     ARG_CHECK(x && t && rows > 0 && C > 0 && HW > 0 && rows_per_group > 0);
     if (!(HW == 1 || HW == 2 || HW == 4 || HW == 8 || HW == 16) || (C * HW) % 16 != 0 || rows % rows_per_group != 0 ||
         rows_per_group > 2 * kBnThreads || rows / rows_per_group > 65535) {
@@ -185,6 +211,21 @@ GEOCB_API int geocb_bn_relu_jvp(float* x, float* t, int64_t rows, int C, int HW,
     const dim3 grid((unsigned)(C * HW / 16), (unsigned)(rows / rows_per_group));
     cudaStream_t st = (cudaStream_t)stream;
     const int cpb = 16 / HW, ld = C * HW;
-    if (rows_per_group <= kBnThreads) return launch_bn<1>(cpb, grid, st, x, t, rows_per_group, ld, pre_bias, weight, bias, eps, relu);
-    return launch_bn<2>(cpb, grid, st, x, t, rows_per_group, ld, pre_bias, weight, bias, eps, relu);
+    if (rows_per_group <= kBnThreads)
+        return launch_bn<1>(cpb, grid, st, x, t, rows_per_group, ld, pre_bias, weight, bias, eps, relu, img, img_row_t);
+    return launch_bn<2>(cpb, grid, st, x, t, rows_per_group, ld, pre_bias, weight, bias, eps, relu, img, img_row_t);
+}
+
+GEOCB_API int geocb_bn_relu_jvp(float* x, float* t, int64_t rows, int C, int HW, int rows_per_group,
+                                const float* pre_bias, const float* weight, const float* bias, float eps, int relu,
+                                void* stream) {
+    return bn_impl(x, t, rows, C, HW, rows_per_group, pre_bias, weight, bias, eps, relu, nullptr, 0, stream);
+}
+
+GEOCB_API int geocb_bn_relu_jvp_to_image(const float* x, const float* t, int64_t rows, int C, int HW, int rows_per_group,
+                                         const float* pre_bias, const float* weight, const float* bias, float eps,
+                                         int relu, float* aimg, int64_t img_row_t, void* stream) {
+    ARG_CHECK(aimg && img_row_t >= rows && rows % 128 == 0 && img_row_t % 128 == 0);
+    return bn_impl((float*)x, (float*)t, rows, C, HW, rows_per_group, pre_bias, weight, bias, eps, relu, aimg, img_row_t,
+                   stream);
 }

@@ -18,6 +18,7 @@
 //                    (A chunks hit L2 three times out of four).
 //   warps            8 = TMA producer (one lane), 9 = MMA issuer (one lane), 0-7 = epilogue (thread = row:
 //                    tcgen05.ld 32 columns -> 128 B of the fp32 row-major C).
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace {
@@ -104,7 +105,8 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 // one thread per (row, 16-byte K-group): hi = tf32(x), lo = x - hi.  rows_per_tile = 128 (A) or 256 (B).
 // TRANS = false: src is row-major [rows][K] (activations); true: src is [K][rows] (weight matrix W[k][n], row = n).
 template <bool TRANS>
-__global__ void gemm3x_split_kernel(const float* __restrict__ src, int64_t rows, int K, int rows_per_tile, float* img) {
+__global__ void gemm3x_split_kernel(const float* __restrict__ src, int64_t rows, int K, int rows_per_tile, float* img,
+                                    int round_lo) {
     const int kgroups = K / 4;
     const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t row = gid % rows;  // consecutive threads = consecutive rows: the image writes coalesce
@@ -120,7 +122,7 @@ __global__ void gemm3x_split_kernel(const float* __restrict__ src, int64_t rows,
     }
     float hi[4], lo[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) hi[i] = to_tf32(v[i]), lo[i] = v[i] - hi[i];
+    for (int i = 0; i < 4; ++i) hi[i] = to_tf32(v[i]), lo[i] = round_lo ? to_tf32(v[i] - hi[i]) : v[i] - hi[i];
     const int nchunks = K / kBK;
     const int64_t tile = row / rows_per_tile;
     const int r = (int)(row % rows_per_tile);
@@ -138,7 +140,7 @@ struct alignas(8) GemmBars {
 };
 
 __global__ void __launch_bounds__(kThreads, 1) gemm3x_kernel(const float* __restrict__ aimg, const float* __restrict__ bimg,
-                                                              int64_t M, int K, int N, float* __restrict__ C) {
+                                                              int64_t M, int K, int N, float* __restrict__ C, int lolo) {
     extern __shared__ __align__(1024) unsigned char smem[];
     GemmBars* bars = (GemmBars*)(smem + kStages * kStageBytes);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -202,6 +204,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm3x_kernel(const float* __rest
                             umma_tf32(d_tmem, umma_desc(a_hi + ao, kLboA), umma_desc(b_hi + bo, kLboB), (c | ks) ? 1u : 0u);
                             umma_tf32(d_tmem, umma_desc(a_lo + ao, kLboA), umma_desc(b_hi + bo, kLboB), 1u);
                             umma_tf32(d_tmem, umma_desc(a_hi + ao, kLboA), umma_desc(b_lo + bo, kLboB), 1u);
+                            if (lolo) umma_tf32(d_tmem, umma_desc(a_lo + ao, kLboA), umma_desc(b_lo + bo, kLboB), 1u);
                         }
                     }
                     umma_commit(&bars->empty[st]);  // stage reusable once these MMAs have read it
@@ -242,6 +245,11 @@ __global__ void __launch_bounds__(kThreads, 1) gemm3x_kernel(const float* __rest
 
 }  // namespace
 
+static int gemm_mode() {
+    const char* e = getenv("GEOCB_GEMM3X_MODE");  // experiment switch: bit 0 = round the lo parts to tf32, bit 1 = add lo.lo
+    return e ? atoi(e) : 0;
+}
+
 GEOCB_API int geocb_gemm3x_supported(int64_t M, int K, int N) {
     return M > 0 && M % kBM == 0 && K > 0 && K % kBK == 0 && N > 0 && N % kBN == 0;
 }
@@ -249,13 +257,13 @@ GEOCB_API int geocb_gemm3x_supported(int64_t M, int K, int N) {
 GEOCB_API int geocb_gemm3x_prep_weights(const float* W, int K, int N, float* bimg, void* stream) {
     ARG_CHECK(W && bimg && K > 0 && K % kBK == 0 && N > 0 && N % kBN == 0);
     const int64_t threads = (int64_t)N * (K / 4);
-    gemm3x_split_kernel<true><<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(W, N, K, kBN, bimg);
+    gemm3x_split_kernel<true><<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(W, N, K, kBN, bimg, gemm_mode() & 1);
     KERNEL_CHECK();
     return 0;
 }
 
 GEOCB_API int geocb_gemm3x(const float* A, int64_t M, int K, int N, const float* bimg, float* aimg, float* C, void* stream) {
-    ARG_CHECK(A && bimg && aimg && C);
+    ARG_CHECK(bimg && aimg && C);  // A == NULL: aimg already holds the operand image (geocb_bn_relu_jvp_to_image)
     if (!geocb_gemm3x_supported(M, K, N)) {
         geocb_set_error("gemm3x needs M %% 256 == 0, K %% 16 == 0, N %% 256 == 0 (got %lld, %d, %d)", (long long)M, K, N);
         return GEOCB_ERR_UNSUPPORTED;
@@ -264,14 +272,16 @@ GEOCB_API int geocb_gemm3x(const float* A, int64_t M, int K, int N, const float*
     DevInfo di;
     int rc = geocb_devinfo(&di);
     if (rc) return rc;
-    const int64_t threads = M * (K / 4);
-    gemm3x_split_kernel<false><<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(A, M, K, 128, aimg);
-    KERNEL_CHECK();
+    if (A) {
+        const int64_t threads = M * (K / 4);
+        gemm3x_split_kernel<false><<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(A, M, K, 128, aimg, gemm_mode() & 1);
+        KERNEL_CHECK();
+    }
     const size_t smem = (size_t)kStages * kStageBytes + sizeof(GemmBars) + 64;
     CU_TRY(cudaFuncSetAttribute(gemm3x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t ntot = (M / kBM) * (N / kBN);
     const unsigned grid = (unsigned)(ntot < di.sm_count ? ntot : di.sm_count);
-    gemm3x_kernel<<<grid, kThreads, smem, st>>>(aimg, bimg, M, K, N, C);
+    gemm3x_kernel<<<grid, kThreads, smem, st>>>(aimg, bimg, M, K, N, C, (gemm_mode() >> 1) & 1);
     KERNEL_CHECK();
     return 0;
 }

@@ -237,14 +237,21 @@ def edge_len_scatter(ja, jb, e_lo, pos_ij, pos_ji, len_out, data):
                                      stream_ptr()), "edge_len_scatter")
 
 
-def bn_relu_jvp(x, t, C_, HW, rows_per_group, pre_bias, weight, bias, eps, relu):
-    """In-place fused BatchNorm(train) JVP (+ReLU) on primal x / tangent t, both [rows, C*HW] contiguous f32.
+def bn_relu_jvp(x, t, C_, HW, rows_per_group, pre_bias, weight, bias, eps, relu, image=None):
+    """Fused BatchNorm(train) JVP (+ReLU) on primal x / tangent t, both [rows, C*HW] contiguous f32: in place, or --
+    with image=(aimg, tangent_row_offset) -- written as the operand image of the tcgen05 GEMM that follows.
     Returns False when the shape is outside what the kernel supports (caller falls back to library ops)."""
     lib = _lib.load()
     rows = x.shape[0]
     if not (HW in (1, 2, 4, 8, 16) and (C_ * HW) % 16 == 0 and rows % rows_per_group == 0 and rows_per_group <= 512
             and rows // rows_per_group <= 65535 and x.is_contiguous() and t.is_contiguous()):
         return False
+    if image is not None:
+        aimg, row_t = image
+        check(lib.geocb_bn_relu_jvp_to_image(ptr(x), ptr(t), rows, C_, HW, rows_per_group, ptr(pre_bias), ptr(weight),
+                                             ptr(bias), float(eps), int(relu), ptr(aimg), int(row_t), stream_ptr()),
+              "bn_relu_jvp_to_image")
+        return True
     check(lib.geocb_bn_relu_jvp(ptr(x), ptr(t), rows, C_, HW, rows_per_group, ptr(pre_bias), ptr(weight), ptr(bias),
                                 float(eps), int(relu), stream_ptr()), "bn_relu_jvp")
     return True
@@ -253,23 +260,40 @@ def bn_relu_jvp(x, t, C_, HW, rows_per_group, pre_bias, weight, bias, eps, relu)
 _gemm3x_weights = {}
 
 
-def gemm3x(a: torch.Tensor, w: torch.Tensor):
-    """a[M,K] @ w[K,N] through the tcgen05 3xTF32 GEMM (fp32-grade), or None when the shape is unsupported.
-    The weight image is built once per weight tensor; the activation image buffer is cached per device."""
+def gemm3x_supported(M, K, N):
+    return bool(_lib.load().geocb_gemm3x_supported(M, K, N))
+
+
+def _gemm3x_weight_image(w):
     lib = _lib.load()
-    M, K = a.shape
-    N = w.shape[1]
-    if not (a.is_contiguous() and w.is_contiguous() and a.dtype == w.dtype == torch.float32
-            and lib.geocb_gemm3x_supported(M, K, N)):
-        return None
+    K, N = w.shape
     key = (w.data_ptr(), K, N)
     if key not in _gemm3x_weights:
         bimg = torch.empty(2 * K * N, dtype=torch.float32, device=w.device)
         check(lib.geocb_gemm3x_prep_weights(ptr(w), K, N, ptr(bimg), stream_ptr()), "gemm3x_prep_weights")
         _gemm3x_weights[key] = (bimg, w)  # keep w alive so the pointer stays unique
-    bimg = _gemm3x_weights[key][0]
-    aimg = _workspace("gemm3x_a", 2 * M * K * 4, a.device)
-    c = torch.empty((M, N), dtype=torch.float32, device=a.device)
+    return _gemm3x_weights[key][0]
+
+
+def gemm3x_image_buffer(M, K, device):
+    """Scratch operand image (tf32 hi | lo tiles) for an [M,K] activation matrix, cached per device."""
+    return _workspace("gemm3x_a", 2 * M * K * 4, device)
+
+
+def gemm3x(a, w: torch.Tensor, M=None):
+    """a[M,K] @ w[K,N] through the tcgen05 3xTF32 GEMM (fp32-grade), or None when the shape is unsupported.
+    `a` is the row-major activation matrix, or None when gemm3x_image_buffer(M, K) already holds its operand image
+    (written by bn_relu_jvp(..., image=...)).  The weight image is built once per weight tensor."""
+    lib = _lib.load()
+    K, N = w.shape
+    M = a.shape[0] if a is not None else M
+    if not (w.is_contiguous() and w.dtype == torch.float32 and lib.geocb_gemm3x_supported(M, K, N)):
+        return None
+    if a is not None and not (a.is_contiguous() and a.dtype == torch.float32 and a.shape[1] == K):
+        return None
+    bimg = _gemm3x_weight_image(w)
+    aimg = gemm3x_image_buffer(M, K, w.device)
+    c = torch.empty((M, N), dtype=torch.float32, device=w.device)
     check(lib.geocb_gemm3x(ptr(a), M, K, N, ptr(bimg), ptr(aimg), ptr(c), stream_ptr()), "gemm3x")
     return c
 

@@ -64,15 +64,27 @@ def _strict_fp32():
 
 
 # ------------------------------------------------------------ tensor-core GEMM for the wide decoder layer
-def _lin(xin: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
-    """xin @ w.  Layers with K >= 256 go through the hand-written tcgen05 3xTF32 GEMM (csrc/jvp_gemm.cu: fp32-grade,
-    ~3x the cuBLAS SIMT SGEMM); GEOCB_JVP_GEMM=cublas keeps the library SGEMM.  Unsupported shapes (a short last
-    batch) use the library GEMM."""
-    if w.shape[0] >= 256 and os.environ.get("GEOCB_JVP_GEMM", "tc") == "tc":
+def _lin(xin: torch.Tensor, w: torch.Tensor, normalised_next: bool) -> torch.Tensor:
+    """xin @ w.  Layers with K >= 256 that feed a BatchNorm go through the hand-written tcgen05 3xTF32 GEMM
+    (csrc/jvp_gemm.cu, 4x the cuBLAS SIMT SGEMM).  Its error is 1.3-1.9e-6 x sum|a||w| (the tensor core's fp32
+    accumulation truncates; rounding the lo parts or adding lo.lo changes nothing, profiles/r2_gemm3x_accuracy.txt)
+    against 3e-7 for SGEMM: harmless in front of a normalisation (median edge-length error 3.8e-7, kink flips 12
+    instead of 9 of 15 641 on s1), but decoders without normalisation keep the library SGEMM.
+    GEOCB_JVP_GEMM=cublas forces the library GEMM everywhere.  Unsupported shapes (a short last batch) fall back too."""
+    if _wants_tc(w, normalised_next):
         y = dg.gemm3x(xin.contiguous(), w)
         if y is not None:
             return y
     return xin @ w
+
+
+def _wants_tc(w, normalised_next):
+    return w.shape[0] >= 256 and normalised_next and os.environ.get("GEOCB_JVP_GEMM", "tc") == "tc"
+
+
+def _bn_fusable(ops, j, n, groups):
+    nxt = ops[j] if j < len(ops) else None
+    return nxt is not None and nxt[0] == "bn" and (nxt[1].training or nxt[1].running_mean is None) and n % groups == 0
 
 
 # ------------------------------------------------------------ explicit forward mode
@@ -293,18 +305,21 @@ def _forward_mode(ops, z, dz, groups):
     n = z.shape[0]
     pending_bias = None  # bias of the last linear map, folded into the fused BN kernel when one follows
     stacked = None       # buffer whose halves x and t currently are (the fused BN kernel works in place on it)
+    in_image = False     # the BN kernel has written the next GEMM's operand image instead of x / t
     i = 0
     while i < len(ops):
         op = ops[i]
         if op[0] == "lin":
-            xin = stacked if stacked is not None else torch.cat([x, t], 0)  # primal and tangent share one GEMM
-            y = _lin(xin, op[1])
+            fusable = _bn_fusable(ops, i + 1, n, groups)
+            if in_image:
+                y = dg.gemm3x(None, op[1], M=2 * n)
+                in_image = False
+            else:
+                xin = stacked if stacked is not None else torch.cat([x, t], 0)  # primal and tangent share one GEMM
+                y = _lin(xin, op[1], fusable)
             x, t = y[:n], y[n:]
             stacked = y
             pending_bias = op[2]
-            nxt = ops[i + 1] if i + 1 < len(ops) else None
-            fusable = (nxt is not None and nxt[0] == "bn" and (nxt[1].training or nxt[1].running_mean is None)
-                       and n % groups == 0)
             if not fusable and pending_bias is not None:
                 x = x + pending_bias
                 pending_bias = None
@@ -314,8 +329,17 @@ def _forward_mode(ops, z, dz, groups):
             relu_next = i + 1 < len(ops) and ops[i + 1][0] == "relu"
             done = False
             if (m.training or m.running_mean is None) and n % groups == 0:
+                # when the layer after this BN(+ReLU) is a wide linear map bound for the tcgen05 GEMM, let the BN
+                # kernel write that GEMM's tf32 hi | lo operand image directly (no row-major round trip, no split pass)
+                j = i + 2 if relu_next else i + 1
+                image = None
+                if (j < len(ops) and ops[j][0] == "lin" and _wants_tc(ops[j][1], _bn_fusable(ops, j + 1, n, groups))
+                        and n % 128 == 0 and ops[j][1].shape[0] == shape[0] * shape[1] * shape[2]
+                        and dg.gemm3x_supported(2 * n, ops[j][1].shape[0], ops[j][1].shape[1])):
+                    image = (dg.gemm3x_image_buffer(2 * n, ops[j][1].shape[0], x.device), n)
                 done = dg.bn_relu_jvp(x, t, shape[0], shape[1] * shape[2], n // groups, pending_bias, m.weight, m.bias,
-                                      m.eps, relu_next)
+                                      m.eps, relu_next, image=image)
+                in_image = done and image is not None
             if done:
                 pending_bias = None
                 if relu_next:
