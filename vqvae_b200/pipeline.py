@@ -89,7 +89,11 @@ def build_codebook_device(z4: torch.Tensor, decoder, k=20, sym="union", K=512, i
     def overlap_decoder_setup():
         # the kNN kernel is in flight (nothing above synchronises): unroll the decoder, build its weight images and
         # create the GEMM handles on a side stream meanwhile instead of in front of the edge-length stage
-        side.wait_stream(torch.cuda.current_stream(dev))
+        import os
+        # measured on B200 (tools/gpu_r2_run15.sh): the side-stream work saves 0.15 s of edge-length set-up but slows
+        # the one-CTA-per-SM kNN filter by 0.3-0.5 s, so it is OFF unless asked for
+        if os.environ.get("GEOCB_OVERLAP_DECODER_SETUP", "0") != "1":
+            return
         with torch.cuda.stream(side):
             warm_up_decoder(decoder, C, batch_size)
 
