@@ -309,20 +309,33 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((buf * C::ATILES + a) * 128);
             const int32_t c0 = (int32_t)(c * kTileRows);
-            float v[4][32];
+            // screen: all four 32-column loads in flight, one wait, four min-trees
+            unsigned below = 0;
+            {
+                float v[4][32];
 #pragma unroll
-            for (int part = 0; part < 4; ++part) tmem_ld32(taddr + part * 32, v[part]);
-            tmem_ld_wait();
+                for (int part = 0; part < 4; ++part) tmem_ld32(taddr + part * 32, v[part]);
+                tmem_ld_wait();
 #pragma unroll
-            for (int part = 0; part < 4; ++part) {
-                float m = v[part][0];
+                for (int part = 0; part < 4; ++part) {
+                    float m = v[part][0];
 #pragma unroll
-                for (int i = 1; i < 32; ++i) m = fminf(m, v[part][i]);
-                if (m < thr) {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        if (v[part][i] < thr) insert(v[part][i], c0 + part * 32 + i);
+                    for (int i = 1; i < 32; ++i) m = fminf(m, v[part][i]);
+                    below |= (m < thr ? 1u : 0u) << part;
                 }
+            }
+            // rare (once the lists have warmed up): re-read the parts that hold a survivor and insert -- kept as ONE
+            // copy of the 32-way insert code (unrolling it four times overflows the instruction cache: 3x slower)
+            below = __reduce_or_sync(0xffffffffu, below);  // tcgen05.ld is warp-collective: the re-read must be uniform
+#pragma unroll 1
+            for (int part = 0; below; ++part, below >>= 1) {
+                if (!(below & 1u)) continue;
+                float w[32];
+                tmem_ld32(taddr + part * 32, w);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                    if (w[i] < thr) insert(w[i], c0 + part * 32 + i);
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
