@@ -32,7 +32,7 @@ def _host_copy(dst: torch.Tensor, src: torch.Tensor, parts=4):
     under torchrun OMP_NUM_THREADS is 1, and one core moves only ~8 GB/s into pinned memory."""
     global _copy_pool
     n = dst.numel()
-    if n < (4 << 20):
+    if n < (4 << 20) or torch.get_num_threads() >= parts:  # torch's own copy is already parallel
         dst.copy_(src)
         return
     if _copy_pool is None:
