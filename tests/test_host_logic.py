@@ -115,44 +115,71 @@ def test_src_shim_standalone():
 @pytest.mark.skipif(not Path("/root/reference/src/training/build_codebook_legacy.py").exists(),
                     reason="needs a checkout of the reference (not present on the GPU box)")
 def test_src_shim_overlays_reference_drivers():
-    """With the reference behind this repo on PYTHONPATH its legacy YAML drivers import unchanged and
-    bind the geodesic functions of this repo; modules this repo does not implement come from the reference."""
+    """With the reference behind this repo on PYTHONPATH: the legacy YAML drivers, the flat VAE and the
+    geodesic functions are this repo's; modules this repo does not implement come from the reference."""
     code = (
         "import importlib, src\n"
         "e = importlib.import_module('src.training.build_codebook_legacy')\n"
         "r = importlib.import_module('src.training.build_riemannian_codebook_legacy')\n"
         "from src.models import VAE, SpatialVAE\n"
         "import src.scripts.build_codebook as cli, src.utils.spatial_latents as u\n"
-        "print(e.__file__, e.build_knn_graph_auto.__module__, e.fit_kmedoids_optimized.__module__,\n"
-        "      r.edge_lengths_riemannian.__module__, r.largest_connected_component.__module__, VAE.__module__,\n"
-        "      SpatialVAE.__module__, cli.__file__, u.__file__)\n")
+        "print(e.build_and_save.__module__, r.build_and_save.__module__, r._reweight_graph_with_riemannian.__module__,\n"
+        "      VAE.__module__, SpatialVAE.__module__, cli.__file__, u.__file__)\n")
     r = _run_py(code, ["/root/reference"])
     assert r.returncode == 0, r.stderr
     out = r.stdout.split()
-    assert out[0] == "/root/reference/src/training/build_codebook_legacy.py"
-    assert out[1:5] == ["vqvae_b200.geo.knn_graph_optimized", "vqvae_b200.geo.kmeans_optimized",
-                        "vqvae_b200.geo.riemannian_metric", "vqvae_b200.geo.knn_graph_optimized"]
-    assert out[5] == "src.models.vae" and out[6] == "vqvae_b200.models.spatial_vae"
-    assert out[7] == str(ROOT / "src" / "scripts" / "build_codebook.py")
-    assert out[8] == "/root/reference/src/utils/spatial_latents.py"
+    assert out[0] == "vqvae_b200.training.build_codebook_legacy"
+    assert out[1] == out[2] == "vqvae_b200.training.build_riemannian_codebook_legacy"
+    assert out[3] == "vqvae_b200.models.vae" and out[4] == "vqvae_b200.models.spatial_vae"
+    assert out[5] == str(ROOT / "src" / "scripts" / "build_codebook.py")
+    assert out[6] == "/root/reference/src/utils/spatial_latents.py"
 
 
-def test_tf32_split_helpers():
-    """The opt-in 3xTF32 GEMM helper: hi part has a 10-bit mantissa, hi+lo is exact, and on a backend without TF32
-    (CPU) the three-GEMM sum is x@w minus only the lo*lo term."""
-    from vqvae_b200.geo import riemannian_metric as rm
-    torch.manual_seed(0)
-    x = torch.randn(64, 512)
-    w = torch.randn(512, 96) / 22
-    xh = rm._tf32_round(x)
-    assert int((xh.view(torch.int32) & 0x1FFF).abs().max()) == 0
-    assert torch.equal(xh + (x - xh), x)
-    assert float(((x - xh).abs() / x.abs()).max()) <= 2.0 ** -11
-    ref = x.double() @ w.double()
-    err3 = float((rm._mm_split3(x, w).double() - ref).abs().max() / ref.abs().max())
-    err1 = float(((x @ w).double() - ref).abs().max() / ref.abs().max())
-    assert err3 < 4 * err1 + 1e-7
-    assert not rm._use_split3(512)  # off unless GEOCB_JVP_3XTF32=1
+def test_legacy_driver_config_plumbing(tmp_path):
+    """Config keys of the legacy YAML drivers (build_codebook_legacy.py:29-41, build_riemannian_codebook_legacy.py:
+    171-197): explicit paths, dataset-based defaults, the three places a checkpoint path may live."""
+    from vqvae_b200.training import _common as C
+    assert str(C.latents_path({"data": {"latents_path": "a/z.pt"}})) == "a/z.pt"
+    assert str(C.latents_path({"data": {"dataset": "CIFAR10 "}})) == "experiments/vae_cifar10/latents_train/z.pt"
+    assert str(C.latents_path({"data": {}})) == "experiments/vae_mnist/latents_train/z.pt"
+    assert str(C.checkpoint_path({"checkpoint_path": "c.pt"})) == "c.pt"
+    assert str(C.checkpoint_path({"vae": {"ckpt_path": "v.pt"}})) == "v.pt"
+    assert str(C.checkpoint_path({"model": {"checkpoint_path": "m.pt"}})) == "m.pt"
+    assert str(C.checkpoint_path({"data": {"dataset": "mnist"}})) == "experiments/vae_mnist/checkpoints/best.pt"
+    assert C.graph_args({"graph": {"k": "10", "metric": "euclidean", "sym": "union", "mode": "distance"}}) == (10, "euclidean", "union", "distance")
+    torch.save({"z": torch.ones(3, 2, dtype=torch.float64)}, tmp_path / "z.pt")
+    assert C.load_latents(tmp_path / "z.pt").dtype == torch.float32
+    torch.save([1, 2], tmp_path / "bad.pt")
+    with pytest.raises(ValueError):
+        C.load_latents(tmp_path / "bad.pt")
+    mask = np.array([True, False, True])
+    assert C.scatter_codes(np.array([4, 5]), mask, 3).tolist() == [4, -1, 5]
+    assert C.scatter_codes(np.array([4, 5, 6]), np.ones(3, bool), 3).tolist() == [4, 5, 6]
+
+
+def test_kink_rule_is_consistent_on_cpu():
+    """tools/kink_margin.py: margins are non-negative, the float64 length matches the oracle, and an edge far from any
+    kink cannot be excused."""
+    import kink_margin
+    import geo_oracle as oracle
+    from conftest import fashion_decoder
+    torch.manual_seed(3)
+    dec = fashion_decoder()
+    a = torch.randn(40, 16)
+    b = a + 0.1 * torch.randn(40, 16)
+    marg = kink_margin.relu_margins(dec, a, b, 512, np.arange(40))
+    L32 = oracle.edge_lengths(dec, a, b, 512).numpy()
+    L64 = np.array([marg[e][2] for e in range(40)])
+    assert all(marg[e][0] >= marg[e][1] >= 0 for e in range(40))
+    assert np.abs(L32 - L64).max() / L64.max() < 1e-4
+    rep = kink_margin.check_edge_lengths(L32, L64, dec, a, b, 512)
+    assert rep["median_rel"] <= 1e-6
+    bad = L64.copy()
+    far = int(np.argmax([marg[e][0] for e in range(40)]))
+    bad[far] *= 1.001
+    if marg[far][1] >= kink_margin.EPS:
+        with pytest.raises(AssertionError):
+            kink_margin.check_edge_lengths(bad, L64, dec, a, b, 512)
 
 
 def test_bench_reference_arm_contract():
@@ -173,7 +200,9 @@ def test_bench_reference_arm_contract():
         assert key in d, key
     assert d["impl"] == "reference" and d["metric"] == "sssp_edge_relax_per_s" and d["unit"] == "edge-relax/s"
     assert d["value"] > 0 and d["e2e"]["value"] == d["value"] and d["e2e"]["h2d_bytes_per_step"] == 0
-    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and "workload" in d["config"]
+    # "reference" when oracle/_ref (the unmodified reference modules, oracle/make_ref.py) travelled with the repo
+    expect = "reference" if (ROOT / "oracle" / "_ref" / "src" / "geo" / "geo_shortest_paths.py").exists() else "port"
+    assert d["cpu_baseline"]["kind"] == expect and d["cpu_baseline"]["cores"] >= 1 and "workload" in d["config"]
     if not torch.cuda.is_available():
         r2 = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--steps", "1", "--warmup", "0", "--images", "80"],
                             env=env, capture_output=True, text=True, timeout=600)

@@ -22,6 +22,7 @@
 // The row image scales with the padded dimension DP in {16, 32, 64}: [hi DP | lo DP | norm/ones 8] floats, 3*DP/8 + 1
 // MMAs per tile pair (7 / 13 / 25).  Shared memory decides the shape: DP=16: two A tiles, 4 B stages; DP=32: two A
 // tiles, 2 stages; DP=64: ONE A tile (68 KB) and the B tile staged in two K-halves (hi | lo+norm, 3 half stages).
+#include <stdlib.h>
 #include "common.cuh"
 #include "knn_tc.cuh"
 
@@ -32,17 +33,24 @@ constexpr int kLBO = kTileRows * 16;        // bytes between K-groups
 constexpr int kL = 32;                      // list length (kq <= 26)
 constexpr int kThreads = 320;
 
-template <int DP_, int ATILES_, int STAGES_, int NSUB_>
+template <int DP_, int ATILES_, int STAGES_, int NSUB_, int NB_>
 struct Cfg {
-    static constexpr int DP = DP_, ATILES = ATILES_, STAGES = STAGES_, NSUB = NSUB_;
+    static constexpr int DP = DP_, ATILES = ATILES_, STAGES = STAGES_, NSUB = NSUB_, NB = NB_;
     static constexpr int kRowFloats = 2 * DP + 8;        // floats per operand row image
     static constexpr int kKGroups = kRowFloats / 4;      // 16-byte K-groups per row
-    static constexpr int kTileBytes = kKGroups * kLBO;   // 20480 / 36864 / 69632
+    static constexpr int kTileBytes = kKGroups * kLBO;   // A tile (128 rows): 20480 / 36864 / 69632
+    static constexpr int kLboB = NB * 16;                // candidate (B) tiles hold NB = 128 or 256 rows: N of the MMA
+    static constexpr int kTileBytesB = kKGroups * kLboB;
     static constexpr int kRowsPerCta = ATILES * kTileRows;
     // B sub-tiles (K-group ranges): one, or [hi) and [lo + norm)
     static constexpr int kSplit = NSUB == 1 ? kKGroups : DP / 4;
-    static constexpr int kStageBytes = (NSUB == 1 ? kKGroups : (kKGroups - DP / 4)) * kLBO;
+    static constexpr int kStageBytes = (NSUB == 1 ? kKGroups : (kKGroups - DP / 4)) * kLboB;
     static constexpr int kSteps = 3 * DP / 8 + 1;
+    static constexpr int NBUF = 512 / (ATILES * NB);     // accumulator buffers per A tile that fit the 512 TMEM columns
+    static_assert(NBUF == 1 || NBUF == 2 || NBUF == 4, "TMEM budget");
+    static constexpr int kBufs = NBUF > 2 ? 2 : NBUF;
+    // D=f32, A=B=tf32, K-major both, M=128, N=NB
+    static constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NB >> 3) << 17) | ((128u >> 4) << 24);
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -84,21 +92,19 @@ __device__ __forceinline__ float to_tf32(float x) {
 }
 // UMMA shared-memory descriptor, K-major, no swizzle (cute::UMMA::SmemDescriptor): start>>4 [0,14),
 // LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), layout_type=0 [61,64)
-__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
-    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | ((uint64_t)(kLBO >> 4) << 16) | ((uint64_t)(128 >> 4) << 32) |
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo) {
+    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(128 >> 4) << 32) |
            (1ULL << 46);
 }
-// instruction descriptor (cute::UMMA::InstrDescriptor): D=f32, A=B=tf32, K-major both, M=128, N=128
-constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
-
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+// (instruction descriptor, cute::UMMA::InstrDescriptor layout: Cfg::kIdesc)
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
         "setp.ne.b32 p, %4, 0;\n"
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
         "}\n" ::"r"(tmem_d),
-        "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate)
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
@@ -124,7 +130,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // byte offset of element (row r, float k) inside a 128-row operand tile image
-__device__ __forceinline__ int img_off(int r, int k) { return (k >> 2) * kLBO + (r >> 3) * 128 + (r & 7) * 16 + (k & 3) * 4; }
+__device__ __forceinline__ int img_off(int r, int k, int lbo) { return (k >> 2) * lbo + (r >> 3) * 128 + (r & 7) * 16 + (k & 3) * 4; }
 // K-group pairs (A kg, B kg) of MMA step t for padded dimension DP: steps are grouped by the B sub-tile they read:
 // first every step on B's hi part (hi.hi and lo.hi per 8-float chunk), then hi.lo per chunk, then ones.norm.
 template <int DP>
@@ -147,10 +153,9 @@ __device__ __forceinline__ void mma_step(int t, int& akg, int& bkg) {
 // one thread per (row, K-group): writes the candidate image (all M rows, padded to whole tiles) and the query image
 // (nq rows of zq, padded to whole CTAs).  Pad candidates get a huge finite norm so they are never kept.
 __global__ void knn_tc_prep_kernel(const float* __restrict__ z, const float* __restrict__ zq, int64_t M, int d, int dp,
-                                   int64_t Mp, int64_t nq, int64_t nq_pad, float* bimg, float* aimg,
+                                   int nb, int64_t Mp, int64_t nq, int64_t nq_pad, float* bimg, float* aimg,
                                    unsigned int* max_nrm_bits) {
     const int kgroups = (2 * dp + 8) / 4, hi_groups = dp / 4;
-    const int64_t tile_floats = (int64_t)kgroups * kLBO / 4;
     const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t row = gid / kgroups;
     const int kg = (int)(gid % kgroups);
@@ -186,16 +191,17 @@ __global__ void knn_tc_prep_kernel(const float* __restrict__ z, const float* __r
             out[1] = 1.f;
         }
     }
-    const int64_t tile = (is_b ? row : qrow) / kTileRows;
-    const int r = (int)((is_b ? row : qrow) % kTileRows);
-    float* base = (is_b ? bimg : aimg) + tile * tile_floats;
-    *(float4*)((char*)base + img_off(r, kg * 4)) = make_float4(out[0], out[1], out[2], out[3]);
+    const int tile_rows = is_b ? nb : kTileRows;  // candidate tiles hold nb rows (the MMA's N), query tiles 128
+    const int64_t tile = (is_b ? row : qrow) / tile_rows;
+    const int r = (int)((is_b ? row : qrow) % tile_rows);
+    float* base = (is_b ? bimg : aimg) + tile * ((int64_t)kgroups * tile_rows * 4);
+    *(float4*)((char*)base + img_off(r, kg * 4, tile_rows * 16)) = make_float4(out[0], out[1], out[2], out[3]);
 }
 
 // ------------------------------------------------------------------ filter ----
 template <int STAGES>
 struct alignas(8) TcBars {
-    uint64_t a_full, full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2];
+    uint64_t a_full, full[STAGES], empty[STAGES], tmem_full[4], tmem_empty[4];  // accumulator barriers: [buffer][A tile]
     uint32_t tmem_base;
 };
 
@@ -204,21 +210,22 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
                                                                      const float* __restrict__ bimg, int64_t Mp,
                                                                      int64_t nq, int32_t* cand_idx, float* cand_thr) {
     constexpr int kTileBytes = C::kTileBytes, kStages = C::STAGES, kRowsPerCta = C::kRowsPerCta, NSUB = C::NSUB;
+    constexpr int NB = C::NB, kBufs = C::kBufs, AT = C::ATILES;
     extern __shared__ __align__(1024) unsigned char smem[];
     unsigned char* a_s = smem;                                   // ATILES A tiles
-    unsigned char* b_s = smem + C::ATILES * kTileBytes;          // kStages B (sub-)tiles
+    unsigned char* b_s = smem + AT * kTileBytes;                 // kStages B (sub-)tiles
     float* sc = (float*)(b_s + kStages * C::kStageBytes);        // [kL][rows] list scores
     int32_t* ix = (int32_t*)(sc + kL * kRowsPerCta);             // [kL][rows] list indices
     TcBars<kStages>* bars = (TcBars<kStages>*)(ix + kL * kRowsPerCta);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int64_t nchunks = Mp / kTileRows;
-    const int64_t tile0 = (int64_t)blockIdx.x * C::ATILES;  // first of this CTA's A tiles
+    const int64_t nchunks = Mp / NB;
+    const int64_t tile0 = (int64_t)blockIdx.x * AT;  // first of this CTA's A tiles
 
     if (tid == 0) {
         mbar_init(&bars->a_full, 1);
         for (int s = 0; s < kStages; ++s) mbar_init(&bars->full[s], 1), mbar_init(&bars->empty[s], 1);
-        for (int b = 0; b < 2; ++b) mbar_init(&bars->tmem_full[b], 1), mbar_init(&bars->tmem_empty[b], 4 * C::ATILES);
+        for (int b = 0; b < 4; ++b) mbar_init(&bars->tmem_full[b], 1), mbar_init(&bars->tmem_empty[b], 4);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 9) {  // one warp allocates all 512 TMEM columns (1 CTA per SM: the shared-memory footprint forces it)
@@ -234,28 +241,30 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
     if (warp == 8) {
         // ===== TMA producer: A tiles once, then the ring of B (sub-)tiles =====
         if (lane == 0) {
-            mbar_expect_tx(&bars->a_full, C::ATILES * kTileBytes);
-            tma_load_1d(a_s, aimg + tile0 * (kTileBytes / 4), C::ATILES * kTileBytes, &bars->a_full);
+            mbar_expect_tx(&bars->a_full, AT * kTileBytes);
+            tma_load_1d(a_s, aimg + tile0 * (kTileBytes / 4), AT * kTileBytes, &bars->a_full);
             for (int64_t it = 0; it < nchunks * NSUB; ++it) {
                 const int64_t c = it / NSUB;
                 const int sub = (int)(it % NSUB);
                 const int st = (int)(it % kStages);
                 const int kg0 = sub == 0 ? 0 : C::kSplit, kg1 = (NSUB == 1 || sub == 1) ? C::kKGroups : C::kSplit;
-                const uint32_t bytes = (uint32_t)((kg1 - kg0) * kLBO);
+                const uint32_t bytes = (uint32_t)((kg1 - kg0) * C::kLboB);
                 mbar_wait(&bars->empty[st], (uint32_t)(((it / kStages) & 1) ^ 1));
                 mbar_expect_tx(&bars->full[st], bytes);
-                tma_load_1d(b_s + st * C::kStageBytes, bimg + c * (kTileBytes / 4) + kg0 * (kLBO / 4), bytes, &bars->full[st]);
+                tma_load_1d(b_s + st * C::kStageBytes, bimg + c * (C::kTileBytesB / 4) + kg0 * (C::kLboB / 4), bytes,
+                            &bars->full[st]);
             }
         }
     } else if (warp == 9) {
-        // ===== MMA issuer =====
+        // ===== MMA issuer.  Accumulators are tracked per (buffer, A tile): with one buffer per A tile (N = 256) the
+        //       epilogue of A tile 0 overlaps the MMAs of A tile 1 and vice versa. =====
         if (lane == 0) {
             mbar_wait(&bars->a_full, 0);
             const uint32_t a_addr = smem_u32(a_s), b_addr = smem_u32(b_s);
             constexpr int kHiSteps = NSUB == 1 ? C::kSteps : 2 * (C::DP / 8);  // steps that read B sub-tile 0
             for (int64_t c = 0; c < nchunks; ++c) {
-                const int buf = (int)(c & 1);
-                mbar_wait(&bars->tmem_empty[buf], (uint32_t)(((c >> 1) & 1) ^ 1));
+                const int buf = (int)(c % kBufs);
+                const uint32_t use = (uint32_t)(c / kBufs);  // how often this buffer has been used before
 #pragma unroll
                 for (int sub = 0; sub < NSUB; ++sub) {
                     const int64_t it = c * NSUB + sub;
@@ -265,22 +274,27 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
                     const int t0 = sub == 0 ? 0 : kHiSteps, t1 = (NSUB == 1 || sub == 1) ? C::kSteps : kHiSteps;
                     const int kg0 = sub == 0 ? 0 : C::kSplit;
 #pragma unroll
-                    for (int a = 0; a < C::ATILES; ++a) {
-                        const uint32_t d_tmem = tmem_base + (uint32_t)((buf * C::ATILES + a) * 128);
+                    for (int a = 0; a < AT; ++a) {
+                        if (sub == 0) {  // the epilogue must have drained this accumulator
+                            mbar_wait(&bars->tmem_empty[buf * AT + a], (use & 1) ^ 1);
+                            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        }
+                        const uint32_t d_tmem = tmem_base + (uint32_t)((buf * AT + a) * NB);
 #pragma unroll
                         for (int t = t0; t < t1; ++t) {
                             int akg, bkg;
                             mma_step<C::DP>(t, akg, bkg);
-                            umma_tf32(d_tmem, umma_desc(a_addr + a * kTileBytes + akg * kLBO),
-                                      umma_desc(b_addr + st * C::kStageBytes + (bkg - kg0) * kLBO), t > 0 ? 1u : 0u);
+                            umma_tf32(d_tmem, umma_desc(a_addr + a * kTileBytes + akg * kLBO, kLBO),
+                                      umma_desc(b_addr + st * C::kStageBytes + (bkg - kg0) * C::kLboB, C::kLboB), C::kIdesc,
+                                      t > 0 ? 1u : 0u);
                         }
+                        if (NSUB == 1 || sub == 1) umma_commit(&bars->tmem_full[buf * AT + a]);  // this accumulator is complete
                     }
                     umma_commit(&bars->empty[st]);  // smem stage reusable once these MMAs have read it
                 }
-                umma_commit(&bars->tmem_full[buf]);  // accumulators of this chunk complete
             }
         }
-    } else if (warp < 4 * C::ATILES) {
+    } else if (warp < 4 * AT) {
         // ===== epilogue: thread = query row =====
         const int a = warp >> 2;  // which A tile; warp%4 selects the TMEM lane quarter this warp may read
         const int row = a * 128 + (warp & 3) * 32 + lane;  // row inside the CTA
@@ -304,42 +318,45 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
             maxpos = mp;
         };
         for (int64_t c = 0; c < nchunks; ++c) {
-            const int buf = (int)(c & 1);
-            mbar_wait(&bars->tmem_full[buf], (uint32_t)((c >> 1) & 1));
+            const int buf = (int)(c % kBufs);
+            mbar_wait(&bars->tmem_full[buf * AT + a], (uint32_t)((c / kBufs) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((buf * C::ATILES + a) * 128);
-            const int32_t c0 = (int32_t)(c * kTileRows);
-            // screen: all four 32-column loads in flight, one wait, four min-trees
-            unsigned below = 0;
-            {
-                float v[4][32];
-#pragma unroll
-                for (int part = 0; part < 4; ++part) tmem_ld32(taddr + part * 32, v[part]);
-                tmem_ld_wait();
-#pragma unroll
-                for (int part = 0; part < 4; ++part) {
-                    float m = v[part][0];
-#pragma unroll
-                    for (int i = 1; i < 32; ++i) m = fminf(m, v[part][i]);
-                    below |= (m < thr ? 1u : 0u) << part;
-                }
-            }
-            // rare (once the lists have warmed up): re-read the parts that hold a survivor and insert -- kept as ONE
-            // copy of the 32-way insert code (unrolling it four times overflows the instruction cache: 3x slower)
-            below = __reduce_or_sync(0xffffffffu, below);  // tcgen05.ld is warp-collective: the re-read must be uniform
+            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((buf * AT + a) * NB);
+            const int32_t c0 = (int32_t)(c * NB);
 #pragma unroll 1
-            for (int part = 0; below; ++part, below >>= 1) {
-                if (!(below & 1u)) continue;
-                float w[32];
-                tmem_ld32(taddr + part * 32, w);
-                tmem_ld_wait();
+            for (int q4 = 0; q4 < NB / 128; ++q4) {  // 128 columns at a time
+                // screen: four 32-column loads in flight, one wait, four min-trees
+                unsigned below = 0;
+                {
+                    float v[4][32];
 #pragma unroll
-                for (int i = 0; i < 32; ++i)
-                    if (w[i] < thr) insert(w[i], c0 + part * 32 + i);
+                    for (int part = 0; part < 4; ++part) tmem_ld32(taddr + q4 * 128 + part * 32, v[part]);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int part = 0; part < 4; ++part) {
+                        float m = v[part][0];
+#pragma unroll
+                        for (int i = 1; i < 32; ++i) m = fminf(m, v[part][i]);
+                        below |= (m < thr ? 1u : 0u) << part;
+                    }
+                }
+                // rare (once the lists have warmed up): re-read the parts that hold a survivor and insert -- kept as ONE
+                // copy of the 32-way insert code (unrolling it four times overflows the instruction cache: 3x slower)
+                below = __reduce_or_sync(0xffffffffu, below);  // tcgen05.ld is warp-collective: the re-read must be uniform
+#pragma unroll 1
+                for (int part = 0; below; ++part, below >>= 1) {
+                    if (!(below & 1u)) continue;
+                    float w[32];
+                    tmem_ld32(taddr + q4 * 128 + part * 32, w);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (w[i] < thr) insert(w[i], c0 + q4 * 128 + part * 32 + i);
+                }
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
-            if (lane == 0) mbar_arrive(&bars->tmem_empty[buf]);
+            if (lane == 0) mbar_arrive(&bars->tmem_empty[buf * AT + a]);
         }
         const int64_t q = (int64_t)blockIdx.x * kRowsPerCta + row;
         if (q < nq) {
@@ -357,10 +374,10 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
 template <class C>
 int launch_tc(const float* z, const float* zq, int64_t M, int d, int64_t nq, float* bimg, float* aimg,
               unsigned int* max_nrm_bits, int32_t* cand_idx, float* cand_thr, cudaStream_t st) {
-    const int64_t Mp = align_up(M, kTileRows), nqp = align_up(nq, C::kRowsPerCta);
+    const int64_t Mp = align_up(M, 256), nqp = align_up(nq, C::kRowsPerCta);  // (256: every config's B tile divides it)
     const int64_t threads = (Mp + nqp) * C::kKGroups;
-    knn_tc_prep_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(z, zq, M, d, C::DP, Mp, nq, nqp, bimg, aimg,
-                                                                           max_nrm_bits);
+    knn_tc_prep_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(z, zq, M, d, C::DP, C::NB, Mp, nq, nqp, bimg,
+                                                                           aimg, max_nrm_bits);
     KERNEL_CHECK();
     const size_t smem = (size_t)C::ATILES * C::kTileBytes + (size_t)C::STAGES * C::kStageBytes +
                         (size_t)kL * C::kRowsPerCta * 8 + sizeof(TcBars<C::STAGES>) + 64;
@@ -371,17 +388,19 @@ int launch_tc(const float* z, const float* zq, int64_t M, int d, int64_t nq, flo
     return 0;
 }
 
-typedef Cfg<16, 2, 4, 1> Cfg16;
-typedef Cfg<32, 2, 2, 1> Cfg32;
-typedef Cfg<64, 1, 3, 2> Cfg64;
+typedef Cfg<16, 2, 4, 1, 128> Cfg16;   // N = 128 MMAs, two accumulator buffers per A tile
+typedef Cfg<16, 2, 3, 1, 256> Cfg16W;  // N = 256 MMAs (half as many instructions), one buffer per A tile
+typedef Cfg<32, 2, 2, 1, 128> Cfg32;
+typedef Cfg<64, 1, 3, 2, 128> Cfg64;
 static_assert(2 * Cfg16::kTileBytes + 4 * Cfg16::kStageBytes + kL * 256 * 8 < 227 * 1024, "smem");
+static_assert(2 * Cfg16W::kTileBytes + 3 * Cfg16W::kStageBytes + kL * 256 * 8 + 512 < 227 * 1024, "smem");
 static_assert(2 * Cfg32::kTileBytes + 2 * Cfg32::kStageBytes + kL * 256 * 8 < 227 * 1024, "smem");
 static_assert(1 * Cfg64::kTileBytes + 3 * Cfg64::kStageBytes + kL * 128 * 8 < 227 * 1024, "smem");
 
 }  // namespace
 
 int knn_tc_dp(int d) { return d <= 16 ? 16 : d <= 32 ? 32 : 64; }
-int64_t knn_tc_padded_candidates(int64_t M) { return align_up(M, kTileRows); }
+int64_t knn_tc_padded_candidates(int64_t M) { return align_up(M, 256); }
 int64_t knn_tc_padded_queries(int64_t nq, int d) { return align_up(nq, d <= 32 ? 256 : 128); }
 int64_t knn_tc_image_floats(int64_t rows_padded, int d) { return rows_padded * (2 * knn_tc_dp(d) + 8); }
 
@@ -392,7 +411,11 @@ int knn_filter_tc(const float* z, const float* zq, int64_t M, int d, int64_t nq,
         return GEOCB_ERR_UNSUPPORTED;
     }
     switch (knn_tc_dp(d)) {
-        case 16: return launch_tc<Cfg16>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
+        case 16: {
+            const char* e = getenv("GEOCB_KNN_TC_N");  // 128 | 256 (default): N of the tcgen05.mma instructions at d <= 16
+            if (e && atoi(e) == 128) return launch_tc<Cfg16>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
+            return launch_tc<Cfg16W>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
+        }
         case 32: return launch_tc<Cfg32>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
         default: return launch_tc<Cfg64>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
     }
