@@ -405,27 +405,21 @@ def run_b200(a):
 
     # ---- end-to-end through the PUBLIC call the reference's callers bind: dijkstra_multi_source(W_scipy, sources)
     #      (src/geo/geo_shortest_paths.py:24-50): host CSR in, host (S,n) float32 out, every copy inside the timed
-    #      region.  N>1: rank 0 uploads and validates the graph once per step and broadcasts it over NVLink (NCCL);
-    #      every rank then runs its own sources and downloads its own rows. ----
+    #      region.  N>1: the upload is split across the ranks (1/N of the CSR per PCIe link + NCCL all-gather over
+    #      NVLink); every rank then runs its own sources and downloads its own rows. ----
     e2e = e2e_dev = None
     if not a.skip_e2e:
         from vqvae_b200.geo import geo_shortest_paths as gsp
-        W_host = g.to_scipy() if (world == 1 or rank == 0) else None
+        W_host = g.to_scipy()  # every rank holds the host matrix (the caller's data), as in an SPMD launch
 
         def e2e_step(i):
             src = step_sources(i)
             if world == 1:
                 Dh = gsp.dijkstra_multi_source(W_host, src)
                 return float(Dh[0, 0])
-            if rank == 0:
-                gg = gsp.graph_to_device(W_host)
-                parts = [gg.indptr, gg.indices, gg.data]
-            else:
-                parts = [torch.empty(n + 1, dtype=torch.int64, device=dev), torch.empty(nnz, dtype=torch.int32, device=dev),
-                         torch.empty(nnz, dtype=torch.float32, device=dev)]
-            for t in parts:
-                dist.broadcast(t, src=0)
-            gg = dg.DeviceCSR(parts[0], parts[1], parts[2], n)
+            # each rank uploads 1/N of the CSR over its own PCIe link, NCCL all-gather over NVLink, validation and
+            # symmetry check on every rank; then every rank searches its own sources and downloads its own rows
+            gg = gsp.graph_to_device(W_host, dist_group=dist.group.WORLD)
             Dh = gsp.dijkstra_multi_source(gg, src)
             return float(Dh[0, 0])
 
@@ -446,7 +440,7 @@ def run_b200(a):
                "h2d_bytes_per_step": csr_bytes + S * 8, "d2h_bytes_per_step": int(world * S * n * 4),
                "ms_per_step": float(t2.item()) / a.steps,
                "api": "vqvae_b200.geo.dijkstra_multi_source(scipy CSR, sources) -> numpy (S,n) float32"
-                      + ("" if world == 1 else "; rank 0 uploads, NCCL broadcast of the CSR, per-rank sources")}
+                      + ("" if world == 1 else "; graph_to_device(W, dist_group): 1/N of the CSR uploaded per rank + NCCL all-gather, per-rank sources")}
 
         # previous rounds' figure, one layer below the public API: pinned CSR -> DeviceCSR -> pinned D
         h_indptr = g.indptr.cpu().pin_memory()

@@ -46,6 +46,14 @@ def main():
         med_r, asg_r, qe_r = km.fit_kmedoids_optimized(g, K=96, init="random", seed=5, dist_group=grp)
         med_1, asg_1, qe_1 = km.fit_kmedoids_optimized(g, K=96, init="random", seed=5)
         out["random_init_equal"] = bool(np.array_equal(med_r, med_1) and np.array_equal(asg_r, asg_1) and qe_r == qe_1)
+        # collective upload of a host matrix: 1/world per rank + NCCL all-gather == plain upload, and the public call on it
+        from vqvae_b200.geo import geo_shortest_paths as gsp
+        Wh = g.to_scipy()
+        g_sh = gsp.graph_to_device(Wh, dist_group=grp)
+        out["sharded_upload_equal"] = bool(torch.equal(g_sh.indptr, g.indptr) and torch.equal(g_sh.indices, g.indices)
+                                           and torch.equal(g_sh.data, g.data))
+        src = [3, 1000 + rank, 19999]
+        out["sssp_on_sharded_equal"] = bool(np.array_equal(gsp.dijkstra_multi_source(g_sh, src), gsp.dijkstra_multi_source(Wh, src)))
         a_sh = km.assign_points_to_medoids(g, single.medoids, dist_group=grp)
         out["assign_equal"] = bool(np.array_equal(a_sh, single.assign))
         out["qe_equal"] = bool(km.compute_quantization_error(g, single.medoids, single.assign, dist_group=grp) == single.qe)

@@ -23,3 +23,4 @@ def test_two_rank_build_and_sharded_assignment_match_single_gpu():
     res = json.loads(line[len("MULTI_GPU_RESULT "):])
     assert res["world"] == 2 and res["all_ranks_ok"], res
     assert res["build_equal"] and res["random_init_equal"] and res["assign_equal"] and res["qe_equal"], res
+    assert res["sharded_upload_equal"] and res["sssp_on_sharded_equal"], res

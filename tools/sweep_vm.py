@@ -80,6 +80,16 @@ print(f"n={n} nnz={nnz} mean_w={mean_w:.4f} sources={S} peak={peak}", flush=True
 if not a.skip_slot:
     ms, st = timed(lambda: dg.sssp_multi(g, src, slots=16, out=Dref, stats=True, kernel="slot"))
     report("slot-major 16 slots delta=4x", ms, st, True)
+    if a.trace:  # round trace of the last slot-major launch (same stats layout, tail of its workspace)
+        total = _lib.load().geocb_sssp_workspace_bytes(n, 16)
+        tr = [v_ for k_, v_ in dg._ws_cache.items() if k_[0] == "sssp"][0][total - 2048:total].view(torch.int64).cpu().numpy()
+        nr = min(int(tr[7]), 120)
+        t, q = tr[8:8 + 2 * nr:2], tr[9:9 + 2 * nr:2]
+        ts = np.r_[t, tr[6]]
+        print("   last launch, round: popped (slot,vertex) pairs -> us   " +
+              "  ".join(f"{i}:{int(q[i])}->{(ts[i+1]-ts[i])/1e3:.0f}" for i in range(nr)), flush=True)
+        print("   relaxations/s by round (popped x mean degree / round time):  " +
+              "  ".join(f"{i}:{q[i]*nnz/n/max(ts[i+1]-ts[i],1):.0f}G" for i in range(nr)), flush=True)
 else:
     dg.sssp_multi(g, src, slots=16, out=Dref, kernel="slot")
 for lib_path in [None] + [x for x in a.libs.split(",") if x]:

@@ -32,9 +32,11 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+// bounded wait: a protocol bug must trap (error returned to the caller), never hang the device
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    uint32_t ok;
-    do {
+    uint32_t ok = 0;
+    for (uint32_t spin = 0; !ok; ++spin) {
+        if (spin > (1u << 26)) __trap();
         asm volatile(
             "{\n"
             ".reg .pred p;\n"
@@ -44,7 +46,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
             : "=r"(ok)
             : "r"(smem_u32(bar)), "r"(parity)
             : "memory");
-    } while (!ok);
+    }
 }
 // 1-D TMA bulk copy global -> shared, completion counted on the mbarrier
 __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {

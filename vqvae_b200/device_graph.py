@@ -93,6 +93,28 @@ class DeviceCSR:
         return cls(h2d(W.indptr.astype(np.int64, copy=False), device), h2d(W.indices.astype(np.int32, copy=False), device),
                    h2d(W.data.astype(np.float32, copy=False), device), W.shape[0])
 
+    @classmethod
+    def from_scipy_sharded(cls, W, device, dist, group=None):
+        """Collective upload of the SAME host matrix held by every rank of `group`: each rank stages 1/world of the
+        indices / data arrays through its own PCIe link and the pieces are all-gathered over NVLink (NCCL), so the
+        host->device time of a large graph divides by the number of GPUs instead of being paid by every rank."""
+        W = W.tocsr()
+        if not W.has_sorted_indices:
+            W = W.sorted_indices()
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        nnz = int(W.nnz)
+        chunk = max(1, -(-nnz // world))
+        lo, hi = min(nnz, rank * chunk), min(nnz, (rank + 1) * chunk)
+        parts = []
+        for arr, dt, tdt in ((W.indices, np.int32, torch.int32), (W.data, np.float32, torch.float32)):
+            mine = torch.zeros(chunk, dtype=tdt, device=device)
+            if hi > lo:
+                mine[: hi - lo] = h2d(arr[lo:hi].astype(dt, copy=False), device)
+            full = torch.empty(world * chunk, dtype=tdt, device=device)
+            dist.all_gather_into_tensor(full, mine, group=group)
+            parts.append(full[:nnz])
+        return cls(h2d(W.indptr.astype(np.int64, copy=False), device), parts[0], parts[1], W.shape[0])
+
     def to_scipy(self):
         from scipy import sparse
         ip = self.indptr.cpu().numpy()

@@ -28,12 +28,13 @@ def ensure_valid_graph(W: sparse.spmatrix) -> sparse.spmatrix:
     return W.tocsr()
 
 
-def graph_to_device(W, directed: bool = False) -> dg.DeviceCSR:
+def graph_to_device(W, directed: bool = False, dist_group=None) -> dg.DeviceCSR:
     """Validate + upload (or pass through an already device-resident graph).
 
     Same checks and exception types as `ensure_valid_graph` (:13-21); the value checks run on the device next to
     the symmetry test (`geocb_csr_sym_check`) instead of as host passes over the arrays, and scipy's
-    `directed=False` view (edge if either direction is stored, smaller weight wins) is merged on the device."""
+    `directed=False` view (edge if either direction is stored, smaller weight wins) is merged on the device.
+    `dist_group`: the upload is split across the ranks of that torch.distributed group (DeviceCSR.from_scipy_sharded)."""
     if isinstance(W, dg.DeviceCSR):
         return W
     if not sparse.isspmatrix(W):
@@ -41,7 +42,11 @@ def graph_to_device(W, directed: bool = False) -> dg.DeviceCSR:
     if W.shape[0] != W.shape[1]:
         raise ValueError("W must be square")
     dev = _lib.require_cuda()
-    g = dg.DeviceCSR.from_scipy(W, dev)
+    if dist_group is not None:  # collective: every rank of the group holds the same W and makes the same call
+        import torch.distributed as dist
+        g = dg.DeviceCSR.from_scipy_sharded(W, dev, dist, dist_group)
+    else:
+        g = dg.DeviceCSR.from_scipy(W, dev)
     if g.n == 0 or g.nnz == 0:
         return g
     flags, extra = dg.csr_sym_check(g)
