@@ -247,6 +247,11 @@ def run_reference(a):
     _CPU_USE_REF = ref is not None
     kind = "reference" if ref is not None else "port"
     cores = len(os.sched_getaffinity(0))
+    try:  # torchrun exports OMP_NUM_THREADS=1: give sklearn's brute kNN the host cores back
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=cores)
+    except Exception:
+        pass
     M = a.ref_latents
     z = torch.randn(a.images, 16, a.grid, a.grid, generator=torch.Generator().manual_seed(42))
     zf = z.permute(0, 2, 3, 1).reshape(-1, 16)[:M].numpy()
