@@ -334,10 +334,13 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
                     tmem_ld_wait();
 #pragma unroll
                     for (int part = 0; part < 4; ++part) {
-                        float m = v[part][0];
+                        // pairwise tree (depth 5) instead of a 31-long dependent chain: two epilogue warps per scheduler
+                        // cannot hide a serial FMNMX chain (ncu r2: issue slots 21 % busy, tensor pipe 23 %)
 #pragma unroll
-                        for (int i = 1; i < 32; ++i) m = fminf(m, v[part][i]);
-                        below |= (m < thr ? 1u : 0u) << part;
+                        for (int w = 16; w; w >>= 1)
+#pragma unroll
+                            for (int i = 0; i < w; ++i) v[part][i] = fminf(v[part][i], v[part][i + w]);
+                        below |= (v[part][0] < thr ? 1u : 0u) << part;
                     }
                 }
                 // rare (once the lists have warmed up): re-read the parts that hold a survivor and insert -- kept as ONE
