@@ -564,7 +564,8 @@ class VoronoiState:
         self.count += 1
 
     def check(self):
-        """Inserts are asynchronous: surface a non-converged one (round limit) before its result is used."""
+        """Inserts are asynchronous and their 'hit the round limit' flag is sticky: callers check once, after the
+        chain / before the labels are used (kmeans_optimized._seed_kpp, _finish_assign), not per draw."""
         check(_lib.load().geocb_voronoi_check(self.g.n, ptr(self.ws), self.ws.numel(), stream_ptr()), "voronoi_insert")
 
     def draw(self, u):
@@ -578,7 +579,6 @@ class VoronoiState:
             check(lib.geocb_pairwise_plan_host(n, host), "pairwise_plan_host")
             self.plan = torch.from_numpy(np.frombuffer(host, dtype=np.int64).copy()).to(dev)
             self.kpp_ws = torch.empty(lib.geocb_kpp_workspace_bytes(n), dtype=torch.uint8, device=dev)
-        self.check()
         res = (C.c_int64 * 4)()
         check(lib.geocb_kpp_draw(ptr(self.dmin32), ptr(self.is_center), n, float(u), ptr(self.plan), ptr(self.kpp_ws),
                                  self.kpp_ws.numel(), res, stream_ptr()), "kpp_draw")

@@ -46,6 +46,7 @@ def _seed_kpp(state: dg.VoronoiState, K: int, seed: int, insert_last: bool):
         centers.append(int(nxt))
     if insert_last and len(centers) > state.count:
         state.insert(centers[-1])
+    state.check()  # a non-converged insert anywhere in the chain invalidates every later draw
     return centers, exact_draws
 
 
