@@ -26,6 +26,12 @@
 #include "common.cuh"
 #include "knn_tc.cuh"
 
+// Warp-cooperative list insert in the epilogue (default).  -DGEOCB_KNN_NOCOOP restores the per-lane insert it replaced
+// (measured at C2, d=16: 2.48 s per-lane, 2.19 s cooperative; `make knn_nocoop`).
+#ifndef GEOCB_KNN_NOCOOP
+#define GEOCB_KNN_COOP 1
+#endif
+
 namespace {
 
 constexpr int kTileRows = 128;
@@ -199,6 +205,41 @@ __global__ void knn_tc_prep_kernel(const float* __restrict__ z, const float* __r
 }
 
 // ------------------------------------------------------------------ filter ----
+// order-preserving float <-> int map (an involution): lets __reduce_max_sync find the largest list entry
+__device__ __forceinline__ int okey(float f) {
+    const int b = __float_as_int(f);
+    return b ^ ((b >> 31) & 0x7fffffff);
+}
+__device__ __forceinline__ float unkey(int k) { return __int_as_float(k ^ ((k >> 31) & 0x7fffffff)); }
+
+// Warp-cooperative list insert (GEOCB_KNN_COOP layout: lists row-major, sc[row][kL]): for every lane with a pending
+// survivor (s < thr of its row), the 32 lanes load the 32 entries of THAT row's list, one __reduce_max_sync finds the
+// entry to replace, a second one the new threshold -- ~20 warp-wide instructions per survivor instead of a 31-step
+// dependent shared-memory scan by one lane while 31 wait.  Returns the caller's (possibly lowered) threshold.
+__device__ __noinline__ float coop_insert(float* sc, int32_t* ix, int row0w, bool pend, float s, int32_t cidx, float thr) {
+    const int lane = threadIdx.x & 31;
+    unsigned todo = __ballot_sync(0xffffffffu, pend);
+    while (todo) {
+        const int j = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const float sj = __shfl_sync(0xffffffffu, s, j);
+        const int32_t cj = __shfl_sync(0xffffffffu, cidx, j);
+        float* lst = sc + (row0w + j) * kL;
+        int ke = okey(lst[lane]);
+        const int mx = __reduce_max_sync(0xffffffffu, ke);
+        const int pos = __ffs(__ballot_sync(0xffffffffu, ke == mx)) - 1;
+        if (lane == pos) {
+            lst[pos] = sj;
+            ix[(row0w + j) * kL + pos] = cj;
+            ke = okey(sj);
+        }
+        const int mx2 = __reduce_max_sync(0xffffffffu, ke);
+        if (lane == j) thr = unkey(mx2);
+        __syncwarp();
+    }
+    return thr;
+}
+
 template <int STAGES>
 struct alignas(8) TcBars {
     uint64_t a_full, full[STAGES], empty[STAGES], tmem_full[4], tmem_empty[4];  // accumulator barriers: [buffer][A tile]
@@ -299,6 +340,14 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
         const int a = warp >> 2;  // which A tile; warp%4 selects the TMEM lane quarter this warp may read
         const int row = a * 128 + (warp & 3) * 32 + lane;  // row inside the CTA
         float thr = __uint_as_float(F32_INF_BITS);
+#ifdef GEOCB_KNN_COOP
+        const int row0w = a * 128 + (warp & 3) * 32;  // first row of this warp; lists are row-major [row][kL]
+        for (int l = 0; l < kL; ++l) {
+            sc[row * kL + l] = __uint_as_float(F32_INF_BITS);
+            ix[row * kL + l] = -1;
+        }
+        __syncwarp();
+#else
         int maxpos = 0;
         for (int l = 0; l < kL; ++l) {
             sc[l * kRowsPerCta + row] = __uint_as_float(F32_INF_BITS);
@@ -317,6 +366,7 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
             thr = m;
             maxpos = mp;
         };
+#endif
         for (int64_t c = 0; c < nchunks; ++c) {
             const int buf = (int)(c % kBufs);
             mbar_wait(&bars->tmem_full[buf * AT + a], (uint32_t)((c / kBufs) & 1));
@@ -325,6 +375,33 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
             const int32_t c0 = (int32_t)(c * NB);
 #pragma unroll 1
             for (int q4 = 0; q4 < NB / 128; ++q4) {  // 128 columns at a time
+#ifdef GEOCB_KNN_COOP
+                // screen with the values kept in registers; a hit part is searched with one warp vote per column and
+                // every survivor is inserted by the whole warp (coop_insert)
+                float v[4][32];
+#pragma unroll
+                for (int part = 0; part < 4; ++part) tmem_ld32(taddr + q4 * 128 + part * 32, v[part]);
+                tmem_ld_wait();
+#pragma unroll
+                for (int part = 0; part < 4; ++part) {
+                    float t[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) t[i] = fminf(v[part][i], v[part][i + 16]);
+#pragma unroll
+                    for (int w = 8; w; w >>= 1)
+#pragma unroll
+                        for (int i = 0; i < w; ++i) t[i] = fminf(t[i], t[i + w]);
+                    if (__any_sync(0xffffffffu, t[0] < thr)) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            const bool pend = v[part][i] < thr;
+                            if (__any_sync(0xffffffffu, pend))
+                                thr = coop_insert(sc, ix, row0w, pend, v[part][i], c0 + q4 * 128 + part * 32 + i, thr);
+                        }
+                    }
+                }
+            }
+#else
                 // screen: four 32-column loads in flight, one wait, four min-trees
                 unsigned below = 0;
                 {
@@ -357,13 +434,18 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
                         if (w[i] < thr) insert(w[i], c0 + q4 * 128 + part * 32 + i);
                 }
             }
+#endif
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
             if (lane == 0) mbar_arrive(&bars->tmem_empty[buf * AT + a]);
         }
         const int64_t q = (int64_t)blockIdx.x * kRowsPerCta + row;
         if (q < nq) {
+#ifdef GEOCB_KNN_COOP
+            for (int l = 0; l < kL; ++l) cand_idx[q * kL + l] = ix[row * kL + l];
+#else
             for (int l = 0; l < kL; ++l) cand_idx[q * kL + l] = ix[l * kRowsPerCta + row];
+#endif
             cand_thr[q] = thr;
         }
     }

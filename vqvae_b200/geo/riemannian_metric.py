@@ -224,7 +224,7 @@ def _conv_matrix(m, shape):
     if m.groups != 1 or any(isinstance(p, str) for p in (m.padding if isinstance(m.padding, tuple) else (m.padding,))):
         return None
     C, H, W = shape
-    w = m.weight
+    w = m.weight.detach().cpu()  # a few hundred small slice assignments: host tensors, one upload at the end
     (sh, sw), (ph, pw), (dh, dw) = m.stride, m.padding, m.dilation
     kh_n, kw_n = w.shape[2], w.shape[3]
     transposed = isinstance(m, nn.ConvTranspose2d)
@@ -278,7 +278,8 @@ def _unrolled_ops(layers, latent_dim):
                                              m.dilation)
                 oshape = tuple(out.shape[1:])
                 A = out.reshape(k, -1).contiguous()
-            bias = None if m.bias is None else m.bias.view(-1, 1, 1).expand(oshape).reshape(-1).contiguous()
+            A = A.cpu()
+            bias = None if m.bias is None else m.bias.detach().cpu().view(-1, 1, 1).expand(oshape).reshape(-1).contiguous()
             if ops and ops[-1][0] == "lin":
                 # two linear maps in a row (conv_in -> first ConvT): compose once, in fp64, round once
                 _, A0, b0, _ = ops.pop()
@@ -295,7 +296,9 @@ def _unrolled_ops(layers, latent_dim):
             ops.append(("gn", m, shape))
         elif isinstance(m, nn.ReLU):
             ops.append(("relu",))
-    return ops
+    dev = next((p.device for m in layers for p in m.parameters()), torch.device("cpu"))
+    return [("lin", o[1].to(dev).contiguous(), None if o[2] is None else o[2].to(dev), o[3]) if o[0] == "lin" else o
+            for o in ops]
 
 
 def _forward_mode(ops, z, dz, groups):
