@@ -26,22 +26,18 @@
 #include "common.cuh"
 #include "knn_tc.cuh"
 
-// Warp-cooperative list insert in the epilogue (default).  -DGEOCB_KNN_NOCOOP restores the per-lane insert it replaced
-// (measured at C2, d=16: 2.48 s per-lane, 2.19 s cooperative; `make knn_nocoop`).
-#ifndef GEOCB_KNN_NOCOOP
-#define GEOCB_KNN_COOP 1
-#endif
 
 namespace {
 
 constexpr int kTileRows = 128;
 constexpr int kLBO = kTileRows * 16;        // bytes between K-groups
 constexpr int kL = 32;                      // list length (kq <= 26)
-constexpr int kThreads = 320;
 
-template <int DP_, int ATILES_, int STAGES_, int NSUB_, int NB_>
+template <int DP_, int ATILES_, int STAGES_, int NSUB_, int NB_, int ES_>
 struct Cfg {
-    static constexpr int DP = DP_, ATILES = ATILES_, STAGES = STAGES_, NSUB = NSUB_, NB = NB_;
+    static constexpr int DP = DP_, ATILES = ATILES_, STAGES = STAGES_, NSUB = NSUB_, NB = NB_, ES = ES_;
+    // ES epilogue warps share each 32-row block (each takes NB/ES of a chunk's columns)
+    static constexpr int kEpiWarps = 4 * ATILES * ES, kThreads = (kEpiWarps + 2) * 32;
     static constexpr int kRowFloats = 2 * DP + 8;        // floats per operand row image
     static constexpr int kKGroups = kRowFloats / 4;      // 16-byte K-groups per row
     static constexpr int kTileBytes = kKGroups * kLBO;   // A tile (128 rows): 20480 / 36864 / 69632
@@ -212,10 +208,12 @@ __device__ __forceinline__ int okey(float f) {
 }
 __device__ __forceinline__ float unkey(int k) { return __int_as_float(k ^ ((k >> 31) & 0x7fffffff)); }
 
-// Warp-cooperative list insert (GEOCB_KNN_COOP layout: lists row-major, sc[row][kL]): for every lane with a pending
-// survivor (s < thr of its row), the 32 lanes load the 32 entries of THAT row's list, one __reduce_max_sync finds the
-// entry to replace, a second one the new threshold -- ~20 warp-wide instructions per survivor instead of a 31-step
-// dependent shared-memory scan by one lane while 31 wait.  Returns the caller's (possibly lowered) threshold.
+// Warp-cooperative list insert (lists row-major, sc[row][kL]): for every lane with a pending survivor (s < its row
+// threshold), the 32 lanes load the 32 entries of THAT row's list, one __reduce_max_sync finds the entry to replace, a
+// second one the new threshold -- ~20 warp-wide instructions per survivor instead of a 31-step dependent shared-memory
+// scan by one lane while 31 wait.  Kept small and out of line on purpose: it is called from 128 unrolled sites with ~130
+// live registers, and a callee that needs many registers makes every call spill them (measured: 2x slower).
+// The caller holds the row block's lock when two warps share the rows.  Returns the caller's (lowered) threshold.
 __device__ __noinline__ float coop_insert(float* sc, int32_t* ix, int row0w, bool pend, float s, int32_t cidx, float thr) {
     const int lane = threadIdx.x & 31;
     unsigned todo = __ballot_sync(0xffffffffu, pend);
@@ -244,20 +242,23 @@ template <int STAGES>
 struct alignas(8) TcBars {
     uint64_t a_full, full[STAGES], empty[STAGES], tmem_full[4], tmem_empty[4];  // accumulator barriers: [buffer][A tile]
     uint32_t tmem_base;
+    int lock[8];  // one per 32-row block of the CTA (epilogue warps sharing the block's lists)
 };
 
 template <class C>
-__global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float* __restrict__ aimg,
-                                                                     const float* __restrict__ bimg, int64_t Mp,
-                                                                     int64_t nq, int32_t* cand_idx, float* cand_thr) {
+__global__ void __launch_bounds__(C::kThreads, 1) knn_filter_tc_kernel(const float* __restrict__ aimg,
+                                                                        const float* __restrict__ bimg, int64_t Mp,
+                                                                        int64_t nq, int32_t* cand_idx, float* cand_thr) {
     constexpr int kTileBytes = C::kTileBytes, kStages = C::STAGES, kRowsPerCta = C::kRowsPerCta, NSUB = C::NSUB;
-    constexpr int NB = C::NB, kBufs = C::kBufs, AT = C::ATILES;
+    constexpr int NB = C::NB, kBufs = C::kBufs, AT = C::ATILES, ES = C::ES;
+    constexpr int kProducer = C::kEpiWarps, kIssuer = C::kEpiWarps + 1;
     extern __shared__ __align__(1024) unsigned char smem[];
     unsigned char* a_s = smem;                                   // ATILES A tiles
     unsigned char* b_s = smem + AT * kTileBytes;                 // kStages B (sub-)tiles
-    float* sc = (float*)(b_s + kStages * C::kStageBytes);        // [kL][rows] list scores
-    int32_t* ix = (int32_t*)(sc + kL * kRowsPerCta);             // [kL][rows] list indices
-    TcBars<kStages>* bars = (TcBars<kStages>*)(ix + kL * kRowsPerCta);
+    float* sc = (float*)(b_s + kStages * C::kStageBytes);        // [rows][kL] list scores
+    int32_t* ix = (int32_t*)(sc + kL * kRowsPerCta);             // [rows][kL] list indices
+    float* thr_s = (float*)(ix + kL * kRowsPerCta);              // [rows] current list maximum (the row's threshold)
+    TcBars<kStages>* bars = (TcBars<kStages>*)(thr_s + kRowsPerCta);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int64_t nchunks = Mp / NB;
@@ -266,10 +267,16 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
     if (tid == 0) {
         mbar_init(&bars->a_full, 1);
         for (int s = 0; s < kStages; ++s) mbar_init(&bars->full[s], 1), mbar_init(&bars->empty[s], 1);
-        for (int b = 0; b < 4; ++b) mbar_init(&bars->tmem_full[b], 1), mbar_init(&bars->tmem_empty[b], 4);
+        for (int b = 0; b < 4; ++b) mbar_init(&bars->tmem_full[b], 1), mbar_init(&bars->tmem_empty[b], 4 * ES);
+        for (int b = 0; b < 8; ++b) bars->lock[b] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 9) {  // one warp allocates all 512 TMEM columns (1 CTA per SM: the shared-memory footprint forces it)
+    for (int i = tid; i < kL * kRowsPerCta; i += C::kThreads) {
+        sc[i] = __uint_as_float(F32_INF_BITS);
+        ix[i] = -1;
+    }
+    for (int i = tid; i < kRowsPerCta; i += C::kThreads) thr_s[i] = __uint_as_float(F32_INF_BITS);
+    if (warp == kIssuer) {  // one warp allocates all 512 TMEM columns (1 CTA per SM: the shared-memory footprint forces it)
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&bars->tmem_base))
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -279,7 +286,7 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *(volatile uint32_t*)&bars->tmem_base;
 
-    if (warp == 8) {
+    if (warp == kProducer) {
         // ===== TMA producer: A tiles once, then the ring of B (sub-)tiles =====
         if (lane == 0) {
             mbar_expect_tx(&bars->a_full, AT * kTileBytes);
@@ -296,7 +303,7 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
                             &bars->full[st]);
             }
         }
-    } else if (warp == 9) {
+    } else if (warp == kIssuer) {
         // ===== MMA issuer.  Accumulators are tracked per (buffer, A tile): with one buffer per A tile (N = 256) the
         //       epilogue of A tile 0 overlaps the MMAs of A tile 1 and vice versa. =====
         if (lane == 0) {
@@ -335,55 +342,33 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
                 }
             }
         }
-    } else if (warp < 4 * AT) {
-        // ===== epilogue: thread = query row =====
-        const int a = warp >> 2;  // which A tile; warp%4 selects the TMEM lane quarter this warp may read
-        const int row = a * 128 + (warp & 3) * 32 + lane;  // row inside the CTA
+    } else {
+        // ===== epilogue: thread = query row; ES warps share a 32-row block, each screens NB/ES columns of a chunk =====
+        const int a = warp / (4 * ES);      // which A tile; warp % 4 selects the TMEM lane quarter this warp may read
+        const int h = (warp >> 2) % ES;     // which slice of the chunk's columns
+        const int row0w = a * 128 + (warp & 3) * 32;  // first row of this warp
+        const int row = row0w + lane;
+        int* lock = ES > 1 ? &bars->lock[row0w >> 5] : nullptr;
+        constexpr int kCols = NB / ES;      // columns per warp and chunk (64, 128 or 256)
+        constexpr int kGroup = kCols >= 128 ? 4 : kCols / 32;  // 32-column loads in flight per wait
         float thr = __uint_as_float(F32_INF_BITS);
-#ifdef GEOCB_KNN_COOP
-        const int row0w = a * 128 + (warp & 3) * 32;  // first row of this warp; lists are row-major [row][kL]
-        for (int l = 0; l < kL; ++l) {
-            sc[row * kL + l] = __uint_as_float(F32_INF_BITS);
-            ix[row * kL + l] = -1;
-        }
-        __syncwarp();
-#else
-        int maxpos = 0;
-        for (int l = 0; l < kL; ++l) {
-            sc[l * kRowsPerCta + row] = __uint_as_float(F32_INF_BITS);
-            ix[l * kRowsPerCta + row] = -1;
-        }
-        auto insert = [&](float s, int32_t cidx) {
-            sc[maxpos * kRowsPerCta + row] = s;
-            ix[maxpos * kRowsPerCta + row] = cidx;
-            float m = sc[row];
-            int mp = 0;
-#pragma unroll 8
-            for (int l = 1; l < kL; ++l) {
-                const float v = sc[l * kRowsPerCta + row];
-                if (v > m) m = v, mp = l;
-            }
-            thr = m;
-            maxpos = mp;
-        };
-#endif
         for (int64_t c = 0; c < nchunks; ++c) {
             const int buf = (int)(c % kBufs);
             mbar_wait(&bars->tmem_full[buf * AT + a], (uint32_t)((c / kBufs) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((buf * AT + a) * NB);
-            const int32_t c0 = (int32_t)(c * NB);
+            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((buf * AT + a) * NB + h * kCols);
+            const int32_t c0 = (int32_t)(c * NB + h * kCols);
+            if (ES > 1) thr = fminf(thr, *(volatile float*)&thr_s[row]);  // the partner warp may have tightened it
 #pragma unroll 1
-            for (int q4 = 0; q4 < NB / 128; ++q4) {  // 128 columns at a time
-#ifdef GEOCB_KNN_COOP
-                // screen with the values kept in registers; a hit part is searched with one warp vote per column and
-                // every survivor is inserted by the whole warp (coop_insert)
-                float v[4][32];
+            for (int q4 = 0; q4 < kCols / (32 * kGroup); ++q4) {
+                // screen with the values kept in registers: kGroup 32-column loads in flight, one wait, min-trees; a hit
+                // part is searched with one warp vote per column and every survivor is inserted by the whole warp
+                float v[kGroup][32];
 #pragma unroll
-                for (int part = 0; part < 4; ++part) tmem_ld32(taddr + q4 * 128 + part * 32, v[part]);
+                for (int part = 0; part < kGroup; ++part) tmem_ld32(taddr + (q4 * kGroup + part) * 32, v[part]);
                 tmem_ld_wait();
 #pragma unroll
-                for (int part = 0; part < 4; ++part) {
+                for (int part = 0; part < kGroup; ++part) {
                     float t[16];
 #pragma unroll
                     for (int i = 0; i < 16; ++i) t[i] = fminf(v[part][i], v[part][i + 16]);
@@ -392,66 +377,45 @@ __global__ void __launch_bounds__(kThreads, 1) knn_filter_tc_kernel(const float*
 #pragma unroll
                         for (int i = 0; i < w; ++i) t[i] = fminf(t[i], t[i + w]);
                     if (__any_sync(0xffffffffu, t[0] < thr)) {
+                        if (ES > 1) {  // the partner warp shares these rows' lists: take the block's lock, refresh thr
+                            if (lane == 0)
+                                while (atomicCAS(lock, 0, 1) != 0) {
+                                }
+                            __syncwarp();
+                            __threadfence_block();
+                            thr = *(volatile float*)&thr_s[row];
+                        }
+                        const float thr_before = thr;
 #pragma unroll
                         for (int i = 0; i < 32; ++i) {
                             const bool pend = v[part][i] < thr;
                             if (__any_sync(0xffffffffu, pend))
-                                thr = coop_insert(sc, ix, row0w, pend, v[part][i], c0 + q4 * 128 + part * 32 + i, thr);
+                                thr = coop_insert(sc, ix, row0w, pend, v[part][i], c0 + (q4 * kGroup + part) * 32 + i, thr);
+                        }
+                        if (thr != thr_before) thr_s[row] = thr;  // publish: final write-out and (ES > 1) the partner
+                        if (ES > 1) {
+                            __threadfence_block();
+                            __syncwarp();
+                            if (lane == 0) atomicExch(lock, 0);
                         }
                     }
                 }
             }
-#else
-                // screen: four 32-column loads in flight, one wait, four min-trees
-                unsigned below = 0;
-                {
-                    float v[4][32];
-#pragma unroll
-                    for (int part = 0; part < 4; ++part) tmem_ld32(taddr + q4 * 128 + part * 32, v[part]);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int part = 0; part < 4; ++part) {
-                        // pairwise tree (depth 5) instead of a 31-long dependent chain: two epilogue warps per scheduler
-                        // cannot hide a serial FMNMX chain (ncu r2: issue slots 21 % busy, tensor pipe 23 %)
-#pragma unroll
-                        for (int w = 16; w; w >>= 1)
-#pragma unroll
-                            for (int i = 0; i < w; ++i) v[part][i] = fminf(v[part][i], v[part][i + w]);
-                        below |= (v[part][0] < thr ? 1u : 0u) << part;
-                    }
-                }
-                // rare (once the lists have warmed up): re-read the parts that hold a survivor and insert -- kept as ONE
-                // copy of the 32-way insert code (unrolling it four times overflows the instruction cache: 3x slower)
-                below = __reduce_or_sync(0xffffffffu, below);  // tcgen05.ld is warp-collective: the re-read must be uniform
-#pragma unroll 1
-                for (int part = 0; below; ++part, below >>= 1) {
-                    if (!(below & 1u)) continue;
-                    float w[32];
-                    tmem_ld32(taddr + q4 * 128 + part * 32, w);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        if (w[i] < thr) insert(w[i], c0 + q4 * 128 + part * 32 + i);
-                }
-            }
-#endif
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
             if (lane == 0) mbar_arrive(&bars->tmem_empty[buf * AT + a]);
         }
-        const int64_t q = (int64_t)blockIdx.x * kRowsPerCta + row;
-        if (q < nq) {
-#ifdef GEOCB_KNN_COOP
-            for (int l = 0; l < kL; ++l) cand_idx[q * kL + l] = ix[row * kL + l];
-#else
-            for (int l = 0; l < kL; ++l) cand_idx[q * kL + l] = ix[l * kRowsPerCta + row];
-#endif
-            cand_thr[q] = thr;
-        }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 9) {
+    if (tid < kRowsPerCta) {  // every epilogue warp is done: thread = row writes its list out
+        const int64_t q = (int64_t)blockIdx.x * kRowsPerCta + tid;
+        if (q < nq) {
+            for (int l = 0; l < kL; ++l) cand_idx[q * kL + l] = ix[tid * kL + l];
+            cand_thr[q] = thr_s[tid];
+        }
+    }
+    if (warp == kIssuer) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
     }
 }
@@ -465,18 +429,19 @@ int launch_tc(const float* z, const float* zq, int64_t M, int d, int64_t nq, flo
                                                                            aimg, max_nrm_bits);
     KERNEL_CHECK();
     const size_t smem = (size_t)C::ATILES * C::kTileBytes + (size_t)C::STAGES * C::kStageBytes +
-                        (size_t)kL * C::kRowsPerCta * 8 + sizeof(TcBars<C::STAGES>) + 64;
+                        (size_t)kL * C::kRowsPerCta * 8 + (size_t)C::kRowsPerCta * 4 + sizeof(TcBars<C::STAGES>) + 64;
     auto kern = knn_filter_tc_kernel<C>;
     CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)(nqp / C::kRowsPerCta), kThreads, smem, st>>>(aimg, bimg, Mp, nq, cand_idx, cand_thr);
+    kern<<<(unsigned)(nqp / C::kRowsPerCta), C::kThreads, smem, st>>>(aimg, bimg, Mp, nq, cand_idx, cand_thr);
     KERNEL_CHECK();
     return 0;
 }
 
-typedef Cfg<16, 2, 4, 1, 128> Cfg16;   // N = 128 MMAs, two accumulator buffers per A tile
-typedef Cfg<16, 2, 3, 1, 256> Cfg16W;  // N = 256 MMAs (half as many instructions), one buffer per A tile
-typedef Cfg<32, 2, 2, 1, 128> Cfg32;
-typedef Cfg<64, 1, 3, 2, 128> Cfg64;
+typedef Cfg<16, 2, 4, 1, 128, 1> Cfg16;    // N = 128 MMAs, two accumulator buffers per A tile, 8 epilogue warps
+typedef Cfg<16, 2, 4, 1, 128, 2> Cfg16E2;  // the same with 16 epilogue warps: two per 32-row block, 64 columns each
+typedef Cfg<16, 2, 3, 1, 256, 1> Cfg16W;   // N = 256 MMAs (half as many instructions), one buffer per A tile
+typedef Cfg<32, 2, 2, 1, 128, 1> Cfg32;
+typedef Cfg<64, 1, 3, 2, 128, 1> Cfg64;
 static_assert(2 * Cfg16::kTileBytes + 4 * Cfg16::kStageBytes + kL * 256 * 8 < 227 * 1024, "smem");
 static_assert(2 * Cfg16W::kTileBytes + 3 * Cfg16W::kStageBytes + kL * 256 * 8 + 512 < 227 * 1024, "smem");
 static_assert(2 * Cfg32::kTileBytes + 2 * Cfg32::kStageBytes + kL * 256 * 8 < 227 * 1024, "smem");
@@ -501,6 +466,10 @@ int knn_filter_tc(const float* z, const float* zq, int64_t M, int d, int64_t nq,
             // filter is bound by the tensor pipe's sustained tf32 rate, not by instruction count
             const char* e = getenv("GEOCB_KNN_TC_N");
             if (e && atoi(e) == 256) return launch_tc<Cfg16W>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
+            // epilogue warps per 32-row block: GEOCB_KNN_TC_ES=2 splits each block's columns over two warps that share the
+            // lists under a lock -- measured SLOWER at C2 (4.6-5.7 s against 2.2 s: lock contention), kept for experiments
+            const char* es = getenv("GEOCB_KNN_TC_ES");
+            if (es && atoi(es) == 2) return launch_tc<Cfg16E2>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
             return launch_tc<Cfg16>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
         }
         case 32: return launch_tc<Cfg32>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
