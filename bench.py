@@ -339,15 +339,17 @@ def run_b200(a):
     digest = hashlib.sha256(np.ascontiguousarray(np.asarray(res.medoids, dtype=np.int64)).tobytes()
                             + np.ascontiguousarray(res.codes.astype(np.int32)).tobytes()).hexdigest()
     S = a.sources_per_step
-    slots = a.slots if a.slots > 0 else dg.default_slots(n)
+    slots = a.slots if a.slots > 0 else dg.default_slots(n, S)
     slots = max(1, min(slots, S, 32))
     kernel = dg._pick_kernel(a.kernel, S, False)
-    if kernel == "vm":
-        slots = min(S, _lib.load().geocb_sssp_vm_slots())
+    if kernel in ("vm", "vm32"):
+        slots = min(S, 32 if kernel == "vm32" else _lib.load().geocb_sssp_vm_slots())
     row_ptr, adj, mean_w = g.adjacency(False)
     rng = np.random.RandomState(1234 + rank)
     D = torch.empty((S, n), dtype=torch.float32, device=dev)
-    launches_per_step = -(-S // slots)  # lock-step batches of `slots` sources, one persistent launch each
+    # slot-major kernel: ONE persistent launch per step, the S sources stream through `slots` live tables;
+    # vertex-major kernels: one launch per `slots` sources
+    launches_per_step = 1 if kernel == "slot" else -(-S // slots)
 
     def barrier():
         if world > 1:
@@ -456,7 +458,8 @@ def run_b200(a):
         def dev_step(i):
             gg = dg.DeviceCSR(h_indptr.to(dev, non_blocking=True), h_indices.to(dev, non_blocking=True),
                               h_data.to(dev, non_blocking=True), n)
-            dg.sssp_multi_to_host(gg, step_sources(i), h_D, slots=slots, kernel=kernel)
+            # (copy-out batches of 16 rows: the last batch's device->host copy is the exposed one)
+            dg.sssp_multi_to_host(gg, step_sources(i), h_D, slots=a.slots if a.slots > 0 else None, kernel=kernel)
             torch.cuda.synchronize()
 
         dev_step(0)
@@ -491,13 +494,15 @@ def run_b200(a):
     achieved = bytes_per_launch / (launch_ms * 1e-3) / 1e9
     traffic = None
     try:
-        if kernel != "vm" and a.workload == "c2":  # the committed ncu capture is of this kernel on this workload
-            traffic = json.loads((ROOT / "profiles" / "sssp_traffic.json").read_text()).get("dram_bytes_per_launch")
+        if kernel == "slot" and a.workload == "c2":  # the committed ncu capture is of this kernel on this workload
+            tj = json.loads((ROOT / "profiles" / "sssp_traffic.json").read_text())
+            # (captured on a 16-source launch: DRAM bytes scale with the sources a launch carries)
+            traffic = tj.get("dram_bytes_per_launch") * (S / launches_per_step) / tj.get("sources_per_launch", 16)
     except Exception:
         pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
-                "kernel": "sssp_vm_kernel" if kernel == "vm" else "sssp_kernel", "launch_ms": launch_ms, "algorithmic_bytes_per_launch": bytes_per_launch,
+                "kernel": {"vm": "sssp_vm_kernel", "vm32": "sssp_vm32_kernel"}.get(kernel, "sssp_kernel"), "launch_ms": launch_ms, "algorithmic_bytes_per_launch": bytes_per_launch,
                 "relaxations_per_algorithmic_edge": stats_tot["relaxations"] / (a.steps * S * nnz)}
     # ---- CPU baseline: scipy Dijkstra on the very same graph, bounded sample ----
     cpu = cpu_build = None

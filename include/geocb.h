@@ -164,7 +164,12 @@ int64_t geocb_sssp_workspace_bytes(int64_t n, int slots);
  * (geo_shortest_paths.py:36-49).  S independent single-source problems solved by a
  * near-far (delta-stepping) frontier relaxation that accumulates path sums in fp64
  * exactly like scipy (monotone rounded addition => same fixed point as Dijkstra),
- * `slots` (1..32) sources in flight per cooperative launch; results rounded to f32 at the end.
+ * through `slots` (1..32) live distance tables; results rounded to f32 at the end.
+ * Without predecessors all S sources run in ONE cooperative launch: a table whose source has converged writes its
+ * row out and takes the next source at once, and table i is first seeded in round i*stagger_rounds/slots (0 = all
+ * at once), so the narrow first and last rounds of one source overlap the wide middle rounds of the others
+ * (callers pass the measured rounds per source, stats[4]/S of an earlier call).  With predecessors: batches of
+ * `slots` sources, one launch each.
  * Per relaxation the kernel gathers only a float32 upper bound of dist[v] (exact filter),
  * frontiers are bitmaps swept in vertex order (see csrc/sssp.cu).
  *   out_d32[S,n] f32 (+inf unreachable); out_pred[S,n] int32 or NULL
@@ -173,12 +178,12 @@ int64_t geocb_sssp_workspace_bytes(int64_t n, int slots);
  *   IN-edges: in_row_ptr / in_adj = adjacency pairs of the transposed graph for a directed
  *   (asymmetric) graph, both NULL for a symmetric one.
  * delta > 0 is the bucket width (callers pass 4x the mean edge weight; any value gives the same result).  Syncs.  stats_host (nullable):
- * int64[4] = {edge relaxations, rounds, threshold scans, improvements}.
+ * int64[5] = {edge relaxations, rounds, threshold scans, improvements, sum over sources of the rounds each was live}.
  * Returns GEOCB_ERR_OVERFLOW if the kernel hit its round limit (8n+4096) without converging. */
 int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t n, const int32_t* sources, int S,
-                     double delta, int slots, void* workspace, int64_t workspace_bytes, float* out_d32,
-                     int32_t* out_pred, const int64_t* in_row_ptr, const void* in_adj, int64_t* stats_host,
-                     void* stream);
+                     double delta, int slots, int stagger_rounds, void* workspace, int64_t workspace_bytes,
+                     float* out_d32, int32_t* out_pred, const int64_t* in_row_ptr, const void* in_adj,
+                     int64_t* stats_host, void* stream);
 
 /* Source-vectorised variant of geocb_sssp_multi (csrc/sssp_vm.cu): same results bit for bit, different layout.
  * The geocb_sssp_vm_slots() (=16) sources of a launch sit side by side per vertex (dist[v][16], ub[v][16], one
@@ -194,6 +199,13 @@ int geocb_sssp_vm_blocks(const int64_t* row_ptr, const void* adj, int64_t n, int
 int geocb_sssp_multi_vm(const void* adj, const uint32_t* blk, int B, int64_t n, const int32_t* sources, int S,
                         double delta, int64_t blk_min_active, void* workspace, int64_t workspace_bytes,
                         float* out_d32, int64_t* stats_host, void* stream);
+/* Second generation (csrc/sssp_vm32.cu): 32 sources per launch, the gathered bound table is bf16 (ub[v][32] = 64 B:
+ * an exact filter, ub = bf16 round-up of dist, a candidate is dropped iff its bf16 round-down >= ub), four lanes per
+ * edge with 8 sources each.  Same blk table, same results bit for bit, same stats layout; n <= 2^26. */
+int64_t geocb_sssp_vm32_workspace_bytes(int64_t n);
+int geocb_sssp_multi_vm32(const void* adj, const uint32_t* blk, int B, int64_t n, const int32_t* sources, int S,
+                          double delta, int64_t blk_min_active, void* workspace, int64_t workspace_bytes,
+                          float* out_d32, int64_t* stats_host, void* stream);
 
 /* ------------------------------------------- incremental Voronoi SSSP ----
  * The K-medoids path (kmeans_optimized.py:40-44, 97-100, 125-134) only ever uses

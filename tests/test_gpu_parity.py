@@ -144,6 +144,23 @@ def test_sssp_line_graph_exact(geo):
     assert np.array_equal(geo["sp"].distances_between(W, [0, 1], [2, 4]), [[2, 4], [1, 3]])
 
 
+def test_sssp_streamed_path_graph(geo):
+    """A 300-vertex path (299 hops: hundreds of rounds per source), every vertex a source, through 4 tables: sources
+    finish at very different rounds, so the hand-over happens mid-flight of the others; plus an isolated vertex."""
+    from vqvae_b200 import device_graph as dg
+    n = 301
+    r = np.arange(n - 2)
+    w = (1 + (r % 7)).astype(np.float32)
+    W = sparse.csr_matrix((np.r_[w, w], (np.r_[r, r + 1], np.r_[r + 1, r])), shape=(n, n))
+    g = dg.DeviceCSR.from_scipy(W, torch.device("cuda"))
+    src = np.r_[np.arange(n), [5, 5, 300]]
+    ref = oracle.sssp_multi(W, src)
+    for slots, stagger in ((4, 0), (4, 30), (32, 100), (1, 0)):
+        D = dg.sssp_multi(g, src, slots=slots, stagger=stagger)
+        assert np.array_equal(D.cpu().numpy(), ref), (slots, stagger)
+    assert np.isinf(ref[300][:300]).all() and ref[300][300] == 0
+
+
 def test_sssp_errors_and_variants(geo):
     sp = geo["sp"]
     W = sparse.csr_matrix(np.array([[0, 1, 0], [1, 0, 10], [0, 10, 0]], np.float32))
@@ -198,6 +215,10 @@ def test_sssp_c1_graph_vs_oracle(geo, c1, slots):
     D, st = dg.sssp_multi(g, src, slots=slots, stats=True)
     assert np.array_equal(D.cpu().numpy(), oracle.sssp_multi(W, src))
     assert st["relaxations"] < 3 * 11 * (W.nnz + 20000)  # near-far keeps redundant work small
+    # the 11 sources stream through `slots` tables in one launch; staggered seeding changes the schedule, not the bits
+    for stagger in (0, 5, 40):
+        Ds, sts = dg.sssp_multi(g, src, slots=slots, stats=True, stagger=stagger)
+        assert torch.equal(Ds, D) and sts["stagger"] == stagger and sts["rounds_per_source"] >= 1, stagger
     if slots == 3:
         # sources stream through the slots (11 sources, 3 slots): predecessors are taken at each hand-over,
         # a repeated source is an independent search, and a second call on the reused workspace is clean

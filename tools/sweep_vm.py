@@ -26,6 +26,7 @@ ap.add_argument("--sources", type=int, default=64)
 ap.add_argument("--images", type=int, default=60000)
 ap.add_argument("--trace", action="store_true")
 ap.add_argument("--skip-slot", action="store_true")
+ap.add_argument("--gen", default="16", help="vertex-major generations to sweep: 16 (sssp_vm.cu), 32 (sssp_vm32.cu)")
 ap.add_argument("--libs", default="", help="comma-separated alternative builds of libgeocb.so, swept after the default one")
 a = ap.parse_args()
 
@@ -98,16 +99,20 @@ for lib_path in [None] + [x for x in a.libs.split(",") if x]:
     _lib.LIB_PATH = Path(lib_path)
     _lib.load()
     print(f"--- {lib_path}", flush=True)
-  for B in [int(x) for x in a.blocks.split(",")]:
+  for gen in [int(x) for x in a.gen.split(",")]:
+   wide = gen == 32
+   for B in [int(x) for x in a.blocks.split(",")]:
     for sc in [float(x) for x in a.scales.split(",")]:
         for mf in [int(x) for x in a.minact.split(",")]:
             ms, st = timed(lambda: dg.sssp_multi_vm(g, src, out=D, stats=True, blocks=B, delta=sc * mean_w,
-                                                    blk_min_active=max(1, n // mf)))
-            report(f"vm B={B} delta={sc:g}x minact=n/{mf}", ms, st, bool(torch.equal(D, Dref)))
+                                                    blk_min_active=max(1, n // mf), wide=wide))
+            report(f"vm{gen} B={B} delta={sc:g}x minact=n/{mf}", ms, st, bool(torch.equal(D, Dref)))
             if a.trace:
               if True:
-                    total = _lib.load().geocb_sssp_vm_workspace_bytes(n)
-                    tr = [v_ for k_, v_ in dg._ws_cache.items() if k_[0] == "sssp_vm"][0][total - 2048:total].view(torch.int64).cpu().numpy()
+                    L = _lib.load()
+                    total = L.geocb_sssp_vm32_workspace_bytes(n) if wide else L.geocb_sssp_vm_workspace_bytes(n)
+                    key = "sssp_vm32" if wide else "sssp_vm"
+                    tr = [v_ for k_, v_ in dg._ws_cache.items() if k_[0] == key][0][total - 2048:total].view(torch.int64).cpu().numpy()
                     nr = min(int(tr[7]), 120)
                     t, q = tr[8:8 + 2 * nr:2], tr[9:9 + 2 * nr:2]
                     ts = np.r_[t, tr[6]]

@@ -47,11 +47,13 @@ SIGNATURES = {
     "geocb_adj_count": (_int, [_p, _i64, _p, _pi64, _p]),
     "geocb_adj_fill": (_int, [_p, _p, _p, _i64, _int, _p, _p, _p, _p]),
     "geocb_sssp_workspace_bytes": (_i64, [_i64, _int]),
-    "geocb_sssp_multi": (_int, [_p, _p, _i64, _p, _int, _f64, _int, _p, _i64, _p, _p, _p, _p, _pi64, _p]),
+    "geocb_sssp_multi": (_int, [_p, _p, _i64, _p, _int, _f64, _int, _int, _p, _i64, _p, _p, _p, _p, _pi64, _p]),
     "geocb_sssp_vm_slots": (_int, []),
     "geocb_sssp_vm_workspace_bytes": (_i64, [_i64]),
     "geocb_sssp_vm_blocks": (_int, [_p, _p, _i64, _int, _p, _p]),
     "geocb_sssp_multi_vm": (_int, [_p, _p, _int, _i64, _p, _int, _f64, _i64, _p, _i64, _p, _pi64, _p]),
+    "geocb_sssp_vm32_workspace_bytes": (_i64, [_i64]),
+    "geocb_sssp_multi_vm32": (_int, [_p, _p, _int, _i64, _p, _int, _f64, _i64, _p, _i64, _p, _pi64, _p]),
     "geocb_voronoi_workspace_bytes": (_i64, [_i64]),
     "geocb_voronoi_init": (_int, [_i64, _p, _p, _p, _p, _i64, _p]),
     "geocb_voronoi_insert": (_int, [_p, _p, _i64, _i32, _i32, _f64, _p, _p, _p, _p, _i64, _p]),

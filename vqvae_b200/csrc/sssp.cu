@@ -90,9 +90,12 @@ struct SsspParams {
     uint32_t* dirty;   // [nslots][nwords]
     SlotCtl* ctl;      // [nslots]
     u64* stats;        // [4] counters + round trace; nullable
-    // full-SSSP mode
-    const int32_t* sources;  // [nslots]
-    float* out_d32;          // [nslots][n]
+    // full-SSSP mode: nsources sources stream through the nslots tables (a table that converges writes its row out
+    // and takes the next source at once); table i is first seeded in round i*stagger/nslots
+    const int32_t* sources;  // [nsources]
+    float* out_d32;          // [nsources][n]
+    int nsources;
+    int stagger;
     // voronoi mode
     int voronoi;
     int32_t center, code;
@@ -214,7 +217,8 @@ __global__ void __launch_bounds__(kThreads, GEOCB_SSSP_MINBLOCKS) sssp_kernel(Ss
     const int wlane = threadIdx.x & 31;
     __shared__ double s_thr[kMaxSlots], s_hint[kMaxSlots];
     __shared__ int s_epoch[kMaxSlots], s_done[kMaxSlots], s_need[kMaxSlots];
-    __shared__ int s_flag, s_alldone;
+    __shared__ int s_src[kMaxSlots], s_fin[kMaxSlots], s_seed[kMaxSlots];  // source index a table works on / hands over
+    __shared__ int s_flag, s_alldone, s_next, s_any;
     const uint64_t pol_keep = policy_evict_last();
     const uint64_t pol_stream = policy_evict_first();
 
@@ -233,29 +237,32 @@ __global__ void __launch_bounds__(kThreads, GEOCB_SSSP_MINBLOCKS) sssp_kernel(Ss
     }
     if (threadIdx.x < kMaxSlots) {
         s_epoch[threadIdx.x] = 0;
-        s_done[threadIdx.x] = 0;
+        s_done[threadIdx.x] = !p.voronoi;  // full-SSSP tables start idle and are seeded by the hand-over step
         s_hint[threadIdx.x] = 0.0;
+        s_src[threadIdx.x] = -1;
     }
+    if (threadIdx.x == 0) s_next = 0;
     grid.sync();
     if (gtid < B) {
         const int s = (int)gtid;
-        const int src = p.voronoi ? p.center : p.sources[s];
         SlotCtl c;
         c.thr2[0] = c.thr2[1] = p.delta;
         for (int i = 0; i < 3; ++i) c.scan_min[i] = F32_INF_BITS, c.scan_pushed[i] = 0, c.active[i] = 0;
         c.pad = 0;
         c.work[0] = c.work[1] = c.work[2] = 0;
-        const u64 old = atomicMin(p.dist + (int64_t)s * n + src, 0ULL);
-        if (old != 0ULL) {  // (voronoi: re-inserting an existing centre changes nothing)
-            p.ub[(int64_t)s * p.nub + src] = 0;
-            atomicOr(p.inq[0] + (int64_t)s * nwords + (src >> 5), 1u << (src & 31));
-            c.active[0] = 1;
+        if (p.voronoi) {
+            const int src = p.center;
+            const u64 old = atomicMin(p.dist + src, 0ULL);
+            if (old != 0ULL) {  // (re-inserting an existing centre changes nothing)
+                p.ub[src] = 0;
+                atomicOr(p.inq[0] + (src >> 5), 1u << (src & 31));
+            }
         }
         p.ctl[s] = c;
     }
     grid.sync();
 
-    unsigned n_relax = 0, n_improve = 0, n_rounds = 0, n_scans = 0;
+    unsigned n_relax = 0, n_improve = 0, n_rounds = 0, n_scans = 0, n_slot_rounds = 0;
     const uint2 pad_edge = make_uint2(0u, F32_INF_BITS);
     const int64_t ngroups = nwords / 32;  // grabs per slot
 
@@ -263,6 +270,78 @@ __global__ void __launch_bounds__(kThreads, GEOCB_SSSP_MINBLOCKS) sssp_kernel(Ss
         const int c_cur = round % 3, c_next = (round + 1) % 3, c_clear = (round + 2) % 3;
         uint32_t* inq_cur = (round & 1) ? p.inq[1] : p.inq[0];
         uint32_t* inq_next = (round & 1) ? p.inq[0] : p.inq[1];
+        if (!p.voronoi) {
+            // ---- hand-over (decided identically in every block): an idle table writes the row of the source it has
+            //      finished and is seeded with the next one.  A finished table's frontier and far bitmaps are all-zero
+            //      (that is what "converged" means), so only dist / proc / ub are reset, in the same pass. ----
+            if (threadIdx.x == 0) {
+                int any = 0, next = s_next, live = 0;
+                for (int s = 0; s < B; ++s) live += !s_done[s];
+                for (int s = 0; s < B; ++s) {
+                    s_fin[s] = s_seed[s] = -1;
+                    if (!s_done[s]) continue;
+                    s_fin[s] = s_src[s];
+                    const bool due = s_src[s] >= 0 || round >= (int)(((int64_t)s * p.stagger) / B) || live == 0;
+                    if (next < p.nsources && due) {
+                        s_seed[s] = next++;
+                        ++live;
+                    }
+                    any |= (s_fin[s] >= 0) | (s_seed[s] >= 0);
+                }
+                s_next = next;
+                s_any = any;
+            }
+            __syncthreads();
+            if (s_any) {
+                for (int s = 0; s < B; ++s) {
+                    const int fin = s_fin[s], seed = s_seed[s];
+                    if (fin < 0 && seed < 0) continue;
+                    u64* dist_s = p.dist + (int64_t)s * n;
+                    u64* proc_s = p.proc + (int64_t)s * n;
+                    ub_t* ub_s = p.ub + (int64_t)s * p.nub;
+                    const int64_t srcv = seed >= 0 ? (int64_t)p.sources[seed] : -1;
+                    if (fin >= 0) {
+                        float* out = p.out_d32 + (int64_t)fin * n;
+                        for (int64_t v = gtid; v < n; v += gthreads) {
+                            // (.cg: the previous hand-over of this table read the same addresses)
+                            out[v] = __double2float_rn(__longlong_as_double((long long)ld_cg_u64(dist_s + v)));
+                            if (seed >= 0) {
+                                dist_s[v] = v == srcv ? 0ULL : D64_INF_BITS;
+                                proc_s[v] = D64_INF_BITS;
+                            }
+                        }
+                        if (seed >= 0)
+                            for (int64_t v = gtid; v < p.nub; v += gthreads) ub_s[v] = v == srcv ? (ub_t)0 : UB_INF;
+                    } else if (gtid == 0) {  // first use of the table: everything is +inf already
+                        dist_s[srcv] = 0ULL;
+                        ub_s[srcv] = 0;
+                    }
+                    if (seed >= 0 && gtid == 0) {
+                        atomicOr(inq_cur + (int64_t)s * nwords + (srcv >> 5), 1u << (srcv & 31));
+                        p.ctl[s].thr2[0] = p.ctl[s].thr2[1] = p.delta;
+                    }
+                }
+                __syncthreads();
+                if (threadIdx.x < B && (s_fin[threadIdx.x] >= 0 || s_seed[threadIdx.x] >= 0)) {
+                    const int s = threadIdx.x;
+                    s_src[s] = s_seed[s];
+                    if (s_seed[s] >= 0) s_done[s] = 0, s_epoch[s] = 0, s_hint[s] = 0.0;
+                }
+                grid.sync();
+            }
+        }
+        // ---- termination test (uniform) ----
+        if (threadIdx.x == 0) s_alldone = 1;
+        __syncthreads();
+        if (threadIdx.x < B && !s_done[threadIdx.x]) s_alldone = 0;
+        __syncthreads();
+        if (s_alldone) break;
+        if (round > p.max_rounds) {  // uniform
+            if (gtid == 0) *p.failed = 1;
+            break;
+        }
+        if (threadIdx.x == 0)
+            for (int s = 0; s < B; ++s) n_slot_rounds += !s_done[s];
         if (gtid < B) p.ctl[gtid].active[c_clear] = 0;  // last read before the previous round's grid.sync
         if (gtid == 0) p.ctl[0].work[c_clear] = 0;     // last used before the previous round's grid.sync
         if (threadIdx.x < B) s_thr[threadIdx.x] = ld_cg_f64(&p.ctl[threadIdx.x].thr2[s_epoch[threadIdx.x] & 1]);
@@ -512,19 +591,9 @@ __global__ void __launch_bounds__(kThreads, GEOCB_SSSP_MINBLOCKS) sssp_kernel(Ss
             p.stats[384 + round] = t;
         }
 #endif
-        // ---- termination test (uniform) ----
-        if (threadIdx.x == 0) s_alldone = 1;
-        __syncthreads();
-        if (threadIdx.x < B && !s_done[threadIdx.x]) s_alldone = 0;
-        __syncthreads();
-        if (s_alldone) break;
-        if (round >= p.max_rounds) {  // uniform
-            if (gtid == 0) *p.failed = 1;
-            break;
-        }
     }
 
-    // ---- finalize ----
+    // ---- finalize (full-SSSP rows were written by the hand-over step) ----
     if (p.voronoi) {
         // dmin32 = f32(dmin64); label = code iff the f32 value strictly decreased
         // (reference: argmin over k of float32(D[k,v]), lowest k on ties, kmeans_optimized.py:100)
@@ -535,9 +604,6 @@ __global__ void __launch_bounds__(kThreads, GEOCB_SSSP_MINBLOCKS) sssp_kernel(Ss
                 p.label[v] = p.code;
             }
         }
-    } else {
-        for (int64_t i = gtid; i < (int64_t)B * n; i += gthreads)
-            p.out_d32[i] = __double2float_rn(__longlong_as_double((long long)p.dist[i]));
     }
     if (p.stats) {
         if (gtid == 0) {
@@ -555,6 +621,7 @@ __global__ void __launch_bounds__(kThreads, GEOCB_SSSP_MINBLOCKS) sssp_kernel(Ss
         if (gtid == 0) {
             atomicAdd(p.stats + 1, (u64)n_rounds);
             atomicAdd(p.stats + 2, (u64)n_scans);
+            atomicAdd(p.stats + 4, (u64)n_slot_rounds);  // sum over sources of the rounds they were live
         }
     }
 }
@@ -679,12 +746,13 @@ GEOCB_API int64_t geocb_voronoi_workspace_bytes(int64_t n) {
 }
 
 GEOCB_API int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t n, const int32_t* sources, int S,
-                               double delta, int slots, void* workspace, int64_t workspace_bytes, float* out_d32,
-                               int32_t* out_pred, const int64_t* in_row_ptr, const void* in_adj, int64_t* stats_host,
-                               void* stream) {
+                               double delta, int slots, int stagger_rounds, void* workspace, int64_t workspace_bytes,
+                               float* out_d32, int32_t* out_pred, const int64_t* in_row_ptr, const void* in_adj,
+                               int64_t* stats_host, void* stream) {
     ARG_CHECK(row_ptr && adj && sources && out_d32 && workspace);
     ARG_CHECK((in_row_ptr == nullptr) == (in_adj == nullptr));
     ARG_CHECK(n > 0 && n < (1LL << 31) - 64 && S > 0 && slots >= 1 && slots <= kMaxSlots && delta > 0);
+    ARG_CHECK(stagger_rounds >= 0 && stagger_rounds <= 4096);
     // (adjacency offsets are 32-bit inside the kernel: geocb_adj_count refuses graphs with >= 2^32 pairs)
     WsLayout w = ws_layout(n, slots, true);
     if (workspace_bytes < w.total) {
@@ -697,15 +765,25 @@ GEOCB_API int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t 
     int rc = coop_grid(&grid);
     if (rc) return rc;
     CU_TRY(cudaMemsetAsync(ws + w.stats, 0, kStatsBytes, st));
-    for (int s0 = 0; s0 < S; s0 += slots) {
+    // Distances only: ONE launch, the S sources stream through `slots` live tables.  With predecessors: batches of
+    // `slots` sources, because the predecessor pass reads a table's converged fp64 distances after the launch.
+    const int batch = out_pred ? slots : S;
+    for (int s0 = 0; s0 < S; s0 += batch) {
         SsspParams p;
         fill_params(p, w, ws, row_ptr, adj, n, delta);
-        p.nslots = (S - s0) < slots ? (S - s0) : slots;
+        p.nsources = (S - s0) < batch ? (S - s0) : batch;
+        p.nslots = p.nsources < slots ? p.nsources : slots;
+        p.stagger = out_pred ? 0 : stagger_rounds;
+        {  // the round limit is per source; sources queue up behind each other
+            const int64_t waves = (p.nsources + p.nslots - 1) / p.nslots + 1;
+            const int64_t lim = (int64_t)p.max_rounds * waves + p.stagger;
+            p.max_rounds = (int)(lim < 0x7fffff00 ? lim : 0x7fffff00);
+        }
         p.stats = (u64*)(ws + w.stats);
         p.sources = sources + s0;
         p.out_d32 = out_d32 + (int64_t)s0 * n;
         p.voronoi = 0;
-        if (s0 + slots < S || s0 > 0) CU_TRY(cudaMemsetAsync(ws + w.stats + 64, 0, kStatsBytes - 64, st));  // trace = last launch
+        if (s0 + batch < S || s0 > 0) CU_TRY(cudaMemsetAsync(ws + w.stats + 64, 0, kStatsBytes - 64, st));  // trace = last launch
         void* args[] = {&p};
         CU_TRY(cudaLaunchCooperativeKernel((void*)sssp_kernel, dim3(grid), dim3(kThreads), args, 0, st));
         if (out_pred) {
@@ -715,7 +793,7 @@ GEOCB_API int geocb_sssp_multi(const int64_t* row_ptr, const void* adj, int64_t 
             KERNEL_CHECK();
         }
     }
-    if (stats_host) CU_TRY(cudaMemcpyAsync(stats_host, ws + w.stats, 32, cudaMemcpyDeviceToHost, st));
+    if (stats_host) CU_TRY(cudaMemcpyAsync(stats_host, ws + w.stats, 40, cudaMemcpyDeviceToHost, st));
     int failed = 0;
     CU_TRY(cudaMemcpyAsync(&failed, ws + w.stats + 40, 4, cudaMemcpyDeviceToHost, st));
     CU_TRY(cudaStreamSynchronize(st));

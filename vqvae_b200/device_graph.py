@@ -371,11 +371,13 @@ def _workspace(tag, nbytes, device, zero=False):
     return buf
 
 
-def default_slots(n):
-    """Concurrent sources per launch.  Measured on B200 at n=2.94M: throughput rises up to 16 slots and is flat to 32
-    (profiles/r1_sssp_variant_sweep_delta4.txt); every slot costs 20.4 B per vertex of workspace plus 4 B per vertex of
-    output row, so very large graphs are capped by what is free on the device (a quarter of it at most)."""
-    slots = 16
+def default_slots(n, S=None):
+    """Live distance tables per launch.  Measured on B200 at n=2.94M: throughput rises up to 16 tables and is nearly
+    flat beyond (profiles/r1_sssp_variant_sweep_delta4.txt); 64 sources streamed through 32 tables take 47.2 ms against
+    49.5 ms through 16 (half the rounds, profiles/r2_sssp_streamed_sweep.txt), so calls that say how many sources they
+    bring (S >= 32) get 32.  Every table costs 20.4 B per vertex of workspace, so very large graphs are capped by what
+    is free on the device (a quarter of it at most)."""
+    slots = 32 if (S is not None and S >= 32) else 16
     try:
         free, _ = torch.cuda.mem_get_info()
         slots = int(max(1, min(slots, (free // 4) // max(1, 25 * n))))
@@ -403,6 +405,20 @@ def _delta_feedback(g, unweighted, relax, S):
         g._adj[key] = scale / 2
 
 
+def _stagger_for(g, unweighted, S, slots):
+    """geocb_sssp_multi's stagger_rounds (rounds over which the first seeding of the `slots` tables is spread).
+    Default 0: on the C2 graph spreading the sources' phases LOSES (64 sources, 32 tables: 47.2 ms at 0, 48.7 at 8,
+    50.0 at 12, 51.2 at 16; profiles/r2_sssp_streamed_sweep.txt) -- a round in which every table is in its wide
+    phase runs at 170-180 G relaxations/s, a mixed round at ~120 G/s, so lock-step phases are the better schedule.
+    GEOCB_SSSP_STAGGER overrides; `auto` uses the measured rounds per source of the previous call on this graph."""
+    env = os.environ.get("GEOCB_SSSP_STAGGER")
+    if env is None or S <= slots:
+        return 0
+    if env == "auto":
+        return int(g._adj.get(("rounds_per_source", bool(unweighted)), 12))
+    return max(0, int(env))
+
+
 def vm_default_blocks(n):
     """Destination blocks of the vertex-major kernel: 200 B of randomly accessed state per vertex (dist 128 + ub 64 +
     masks 8), one block's share kept near 40 MB so that it stays L2 resident next to the streamed data."""
@@ -410,12 +426,13 @@ def vm_default_blocks(n):
 
 
 def _pick_kernel(kernel, S, want_pred):
-    """'slot' = csrc/sssp.cu (one table per source), 'vm' = csrc/sssp_vm.cu (16 sources side by side per vertex).
+    """'slot' = csrc/sssp.cu (one table per source), 'vm' = csrc/sssp_vm.cu (16 sources side by side per vertex),
+    'vm32' = csrc/sssp_vm32.cu (32 sources per vertex, bf16 bound table).
     'auto' = 'slot': on the C2 graph the vertex-major kernel shares an edge visit among only 3.8 of its 16 sources
     and measures 66 G edge-relax/s against 125 G/s (profiles/r2_sssp_vm_*.txt); it stays selectable for graphs whose
     sources overlap more.  Predecessors need 'slot'."""
     kernel = kernel or os.environ.get("GEOCB_SSSP_KERNEL", "auto")
-    if kernel not in ("auto", "slot", "vm"):
+    if kernel not in ("auto", "slot", "vm", "vm32"):
         raise ValueError(f"unknown SSSP kernel '{kernel}'")
     if want_pred:
         return "slot"
@@ -423,8 +440,9 @@ def _pick_kernel(kernel, S, want_pred):
 
 
 def sssp_multi_vm(g: DeviceCSR, sources, unweighted=False, delta=None, out=None, stats=False, blocks=None,
-                  blk_min_active=None):
-    """S independent SSSPs through the vertex-major kernel -> D32[S,n] on the device."""
+                  blk_min_active=None, wide=False):
+    """S independent SSSPs through the vertex-major kernel -> D32[S,n] on the device.
+    wide: the 32-source / bf16-bound generation (csrc/sssp_vm32.cu) instead of the 16-source one."""
     lib = _lib.load()
     dev = g.indptr.device
     row_ptr, adj, mean_w = g.adjacency(unweighted)
@@ -437,19 +455,25 @@ def sssp_multi_vm(g: DeviceCSR, sources, unweighted=False, delta=None, out=None,
     if blk_min_active is None:
         # a blocked round scans the n mask words B times; worth it once the popped rows' gathers would thrash L2
         blk_min_active = int(os.environ.get("GEOCB_SSSP_VM_MIN_ACTIVE", max(1, g.n // 16)))
-    ws = _workspace("sssp_vm", lib.geocb_sssp_vm_workspace_bytes(g.n), dev)
+    if wide:
+        ws = _workspace("sssp_vm32", lib.geocb_sssp_vm32_workspace_bytes(g.n), dev)
+        fn, name = lib.geocb_sssp_multi_vm32, "sssp_multi_vm32"
+    else:
+        ws = _workspace("sssp_vm", lib.geocb_sssp_vm_workspace_bytes(g.n), dev)
+        fn, name = lib.geocb_sssp_multi_vm, "sssp_multi_vm"
     D = out if out is not None else torch.empty((S, g.n), dtype=torch.float32, device=dev)
     st = (C.c_int64 * 8)()
-    check(lib.geocb_sssp_multi_vm(ptr(adj), ptr(blk), B, g.n, ptr(src), S, float(delta), int(blk_min_active), ptr(ws),
-                                  ws.numel(), ptr(D), st, stream_ptr()), "sssp_multi_vm")
+    check(fn(ptr(adj), ptr(blk), B, g.n, ptr(src), S, float(delta), int(blk_min_active), ptr(ws),
+             ws.numel(), ptr(D), st, stream_ptr()), name)
     if stats:
         return D, dict(relaxations=st[0], rounds=st[1], scans=st[2], improvements=st[3], edge_visits=st[4],
-                       blocked_rounds=st[5], slots=lib.geocb_sssp_vm_slots(), delta=delta, blocks=B, kernel="vm")
+                       blocked_rounds=st[5], slots=32 if wide else lib.geocb_sssp_vm_slots(), delta=delta, blocks=B,
+                       kernel="vm32" if wide else "vm")
     return D
 
 
 def sssp_multi(g: DeviceCSR, sources, unweighted=False, want_pred=False, delta=None, slots=None, out=None,
-               stats=False, kernel=None, g_in: DeviceCSR | None = None):
+               stats=False, kernel=None, g_in: DeviceCSR | None = None, stagger=None):
     """S independent SSSPs -> D32[S,n] (+pred int32[S,n]) on the device.
     g_in: transpose of a directed (asymmetric) g -- predecessors are searched over in-edges."""
     lib = _lib.load()
@@ -457,29 +481,34 @@ def sssp_multi(g: DeviceCSR, sources, unweighted=False, want_pred=False, delta=N
     row_ptr, adj, mean_w = g.adjacency(unweighted)
     src = torch.as_tensor(np.asarray(sources, dtype=np.int32), device=dev)
     S = int(src.numel())
-    if _pick_kernel(kernel, S, want_pred) == "vm":
-        return sssp_multi_vm(g, sources, unweighted=unweighted, delta=delta, out=out, stats=stats)
+    picked = _pick_kernel(kernel, S, want_pred)
+    if picked in ("vm", "vm32"):
+        return sssp_multi_vm(g, sources, unweighted=unweighted, delta=delta, out=out, stats=stats, wide=picked == "vm32")
     auto_delta = delta is None
     if auto_delta:
         delta = _delta_for(g, mean_w, unweighted)
-    slots = default_slots(g.n) if slots is None else slots
+    slots = default_slots(g.n, None if want_pred else S) if slots is None else slots
     slots = max(1, min(slots, S, 32))
     nbytes = lib.geocb_sssp_workspace_bytes(g.n, slots)
     ws = _workspace("sssp", nbytes, dev)
     D = out if out is not None else torch.empty((S, g.n), dtype=torch.float32, device=dev)
     P = torch.empty((S, g.n), dtype=torch.int32, device=dev) if want_pred else None
-    st = (C.c_int64 * 4)()
+    st = (C.c_int64 * 5)()
     in_ptr = in_adj = None
     if want_pred and g_in is not None:
         in_ptr, in_adj, _ = g_in.adjacency(unweighted)
-    check(lib.geocb_sssp_multi(ptr(row_ptr), ptr(adj), g.n, ptr(src), S, float(delta), slots, ptr(ws), ws.numel(),
-                               ptr(D), ptr(P), ptr(in_ptr), ptr(in_adj), st, stream_ptr()), "sssp_multi")
+    if stagger is None:
+        stagger = 0 if want_pred else _stagger_for(g, unweighted, S, slots)
+    check(lib.geocb_sssp_multi(ptr(row_ptr), ptr(adj), g.n, ptr(src), S, float(delta), slots, int(stagger), ptr(ws),
+                               ws.numel(), ptr(D), ptr(P), ptr(in_ptr), ptr(in_adj), st, stream_ptr()), "sssp_multi")
     if auto_delta:
         _delta_feedback(g, unweighted, st[0], S)
+    if st[4] > 0:
+        g._adj[("rounds_per_source", bool(unweighted))] = max(1, min(4096, round(st[4] / S)))
     res = (D, P) if want_pred else D
     if stats:
         return res, dict(relaxations=st[0], rounds=st[1], scans=st[2], improvements=st[3], slots=slots, delta=delta,
-                         kernel="slot")
+                         kernel="slot", stagger=int(stagger), rounds_per_source=st[4] / S)
     return res
 
 
@@ -495,8 +524,9 @@ def sssp_multi_to_host(g: DeviceCSR, sources, out_host: torch.Tensor, unweighted
     S = int(src.size)
     slots = default_slots(g.n) if slots is None else slots
     slots = max(1, min(slots, S, 32))
-    if _pick_kernel(kernel, S, pred_host is not None) == "vm":
-        slots = min(S, _lib.load().geocb_sssp_vm_slots())  # one launch per batch: the copy-out overlaps the next launch
+    picked = _pick_kernel(kernel, S, pred_host is not None)
+    if picked in ("vm", "vm32"):  # one launch per batch: the copy-out overlaps the next launch
+        slots = min(S, 32 if picked == "vm32" else _lib.load().geocb_sssp_vm_slots())
     assert out_host.shape == (S, g.n) and out_host.dtype == torch.float32 and out_host.device.type == "cpu"
     main = torch.cuda.current_stream(dev)
     side = _side_stream(dev)
