@@ -19,7 +19,7 @@ from . import _lib
 from . import device_graph as dg
 from .sharding import shard_range, all_gather_rows  # noqa: F401  (re-exported)
 from .geo.knn_graph_optimized import knn_graph_device
-from .geo.riemannian_metric import edge_lengths_device, warm_up_decoder
+from .geo.riemannian_metric import decoder_plan, edge_lengths_device, warm_up_decoder
 from .geo.kmeans_optimized import fit_kmedoids_optimized
 
 
@@ -87,15 +87,21 @@ def build_codebook_device(z4: torch.Tensor, decoder, k=20, sym="union", K=512, i
     side = torch.cuda.Stream(device=dev)
 
     def overlap_decoder_setup():
-        # the kNN kernel is in flight (nothing above synchronises): unroll the decoder, build its weight images and
-        # create the GEMM handles on a side stream meanwhile instead of in front of the edge-length stage
+        # the kNN kernel is in flight (nothing above synchronises).  Host-only part of the edge-length set-up goes here,
+        # in its shadow: unrolling the decoder into dense operators (CPU), their upload on a side stream (copy engine,
+        # no SM work) and the creation of the GEMM library handle - 0.15 s that would otherwise sit in front of the
+        # edge-length stage.  Running the decoder once as well (GEOCB_OVERLAP_DECODER_SETUP=1) was measured and
+        # rejected: its kernels slow the one-CTA-per-SM kNN filter by 0.3-0.5 s (tools/gpu_r2_run15.sh).
         import os
-        # measured on B200 (tools/gpu_r2_run15.sh): the side-stream work saves 0.15 s of edge-length set-up but slows
-        # the one-CTA-per-SM kNN filter by 0.3-0.5 s, so it is OFF unless asked for
-        if os.environ.get("GEOCB_OVERLAP_DECODER_SETUP", "0") != "1":
+        mode = os.environ.get("GEOCB_OVERLAP_DECODER_SETUP", "host")
+        if mode == "0":
             return
         with torch.cuda.stream(side):
-            warm_up_decoder(decoder, C, batch_size)
+            if mode == "1":
+                warm_up_decoder(decoder, C, batch_size)
+            else:
+                decoder_plan(decoder, C)
+                torch.cuda.current_blas_handle()
 
     if world == 1:
         g_euc, _, _ = knn_graph_device(z_flat, k_eff, "connectivity", sym, after_launch=overlap_decoder_setup)
