@@ -87,13 +87,15 @@ def build_codebook_device(z4: torch.Tensor, decoder, k=20, sym="union", K=512, i
     side = torch.cuda.Stream(device=dev)
 
     def overlap_decoder_setup():
-        # the kNN kernel is in flight (nothing above synchronises).  Host-only part of the edge-length set-up goes here,
-        # in its shadow: unrolling the decoder into dense operators (CPU), their upload on a side stream (copy engine,
-        # no SM work) and the creation of the GEMM library handle - 0.15 s that would otherwise sit in front of the
-        # edge-length stage.  Running the decoder once as well (GEOCB_OVERLAP_DECODER_SETUP=1) was measured and
-        # rejected: its kernels slow the one-CTA-per-SM kNN filter by 0.3-0.5 s (tools/gpu_r2_run15.sh).
+        # the kNN kernel is in flight (nothing above synchronises): edge-length set-up could run in its shadow.
+        # Measured on B200 and rejected, so OFF unless asked for (GEOCB_OVERLAP_DECODER_SETUP):
+        #   "1"    = run the decoder once on a side stream: saves 0.15 s of set-up, slows the one-CTA-per-SM kNN filter
+        #            by 0.3-0.5 s (tools/gpu_r2_run15.sh);
+        #   "host" = host-only part (unroll the decoder on the CPU, upload the operators through the copy engine, create
+        #            the GEMM library handle): edge_len 2.33 -> 2.27 s, kNN 2.29 -> 2.37-2.41 s, total unchanged
+        #            (tools/gpu_r2_quick.sh).
         import os
-        mode = os.environ.get("GEOCB_OVERLAP_DECODER_SETUP", "host")
+        mode = os.environ.get("GEOCB_OVERLAP_DECODER_SETUP", "0")
         if mode == "0":
             return
         with torch.cuda.stream(side):
