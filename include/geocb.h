@@ -248,6 +248,16 @@ int geocb_kpp_draw(const float* dmin32, const uint8_t* is_center, int64_t n, dou
 int geocb_pairwise_sum_f32(const float* x, int64_t n, int square, int finite_only, void* workspace,
                            int64_t workspace_bytes, float* out_host, int64_t* n_used_host, void* stream);
 
+/* Allocation-free variant of geocb_pairwise_sum_f32 (finite_only = 0).  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Calls no cudaMalloc / cudaFree / allocating library routine: its scratch (summation
+ * plan + partial sums) is a 3 MiB file-scope `static __device__` array that every GPU loading the library holds until
+ * exit.  n <= geocb_pairwise_sum_f32_static_max_n() = 4 194 304 elements, else GEOCB_ERR_WORKSPACE with a message.
+ * All calls on a device share the array: calls that overlap on the GPU race; serialise them.  Same bits as
+ * geocb_pairwise_sum_f32 -> *out_host (syncs the stream). */
+int64_t geocb_pairwise_sum_f32_static_max_n(void);
+int geocb_pairwise_sum_f32_static(const float* x, int64_t n, int square, float* out_host, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -63,6 +63,8 @@ SIGNATURES = {
     "geocb_kpp_workspace_bytes": (_i64, [_i64]),
     "geocb_kpp_draw": (_int, [_p, _p, _i64, _f64, _p, _p, _i64, _pi64, _p]),
     "geocb_pairwise_sum_f32": (_int, [_p, _i64, _int, _int, _p, _i64, C.POINTER(C.c_float), _pi64, _p]),
+    "geocb_pairwise_sum_f32_static_max_n": (_i64, []),
+    "geocb_pairwise_sum_f32_static": (_int, [_p, _i64, _int, C.POINTER(C.c_float), _p]),
 }
 
 _lib = None

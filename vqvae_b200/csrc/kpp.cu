@@ -505,3 +505,85 @@ GEOCB_API int geocb_pairwise_sum_f32(const float* x, int64_t n, int square, int 
     if (comp) cudaFreeAsync(comp, st);
     return rc;
 }
+
+// ------------------------------------------------ allocation-free pairwise sum ----
+// geocb_pairwise_sum_f32_static: geocb_pairwise_sum_f32 (finite_only = 0) for callers that must not allocate device
+// memory (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
+// reference.  Its scratch -- the device copy of the summation plan and the
+// partial sums of the leaves / inner nodes -- lives in a file-scope device array of fixed size, resident on every GPU
+// that loads the library until the process exits.  All calls on a device share that array: calls that overlap on the
+// GPU (different streams, different host threads) race.  Nothing in it has to start at zero: the plan is re-uploaded and
+// every partial-sum slot the tree reads is written by the same call's leaf pass first.
+#define GEOCB_STATIC_SUM_MAX_N (4LL << 20)           /* elements; keep in step with include/geocb.h */
+#define GEOCB_STATIC_SUM_SCRATCH_BYTES (3 << 20)     /* plan <= 2 097 368 B + partial sums <= 524 300 B at the maximum n */
+static __device__ __align__(256) unsigned char g_static_sum_scratch[GEOCB_STATIC_SUM_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_static_sum_ptr[kMaxDevices];  // device address of g_static_sum_scratch, per device (0 = not looked up yet)
+
+// The array's name is a host-side stand-in in host code, not a device address: look the address up once per device,
+// with that device current.
+int static_sum_scratch(void** out) {
+    int dev = -1;
+    CU_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) {
+        geocb_set_error("device ordinal %d outside the %d supported by geocb_pairwise_sum_f32_static", dev, kMaxDevices);
+        return GEOCB_ERR_UNSUPPORTED;
+    }
+    void* p = __atomic_load_n(&g_static_sum_ptr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        CU_TRY(cudaGetSymbolAddress(&p, g_static_sum_scratch));
+        if (!p) {
+            geocb_set_error("cudaGetSymbolAddress returned a null address for the static scratch array");
+            return GEOCB_ERR_UNSUPPORTED;
+        }
+        __atomic_store_n(&g_static_sum_ptr[dev], p, __ATOMIC_RELEASE);  // (same value from every thread that races here)
+    }
+    *out = p;
+    return 0;
+}
+}  // namespace
+
+GEOCB_API int64_t geocb_pairwise_sum_f32_static_max_n(void) { return GEOCB_STATIC_SUM_MAX_N; }
+
+GEOCB_API int geocb_pairwise_sum_f32_static(const float* x, int64_t n, int square, float* out_host, void* stream) {
+    ARG_CHECK(x && out_host && n >= 0);
+    if (n > GEOCB_STATIC_SUM_MAX_N) {
+        geocb_set_error("geocb_pairwise_sum_f32_static: n = %lld exceeds the static scratch limit of %lld elements "
+                        "(use geocb_pairwise_sum_f32)", (long long)n, (long long)GEOCB_STATIC_SUM_MAX_N);
+        return GEOCB_ERR_WORKSPACE;
+    }
+    if (n == 0) {
+        *out_host = 0.f;
+        return 0;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    void* scratch = nullptr;
+    int rc = static_sum_scratch(&scratch);
+    if (rc) return rc;
+    std::vector<int64_t> plan((size_t)plan_words(n));  // (host memory; the device side allocates nothing)
+    plan_fill(n, plan.data());
+    const int64_t plan_bytes = align_up((int64_t)plan.size() * 8, 256);
+    const int64_t vals_bytes = (plan[1] + plan[2] + 2) * 4;
+    if (plan_bytes + vals_bytes > GEOCB_STATIC_SUM_SCRATCH_BYTES) {  // cannot happen for n <= the maximum; belt and braces
+        geocb_set_error("geocb_pairwise_sum_f32_static: n = %lld needs %lld B of scratch, the static array holds %d",
+                        (long long)n, (long long)(plan_bytes + vals_bytes), GEOCB_STATIC_SUM_SCRATCH_BYTES);
+        return GEOCB_ERR_WORKSPACE;
+    }
+    int64_t* plan_dev = (int64_t*)scratch;
+    float* vals = (float*)((char*)scratch + plan_bytes);
+    CU_TRY(cudaMemcpyAsync(plan_dev, plan.data(), plan.size() * 8, cudaMemcpyHostToDevice, st));
+    ElemSrc src;
+    src.mode = square ? SRC_SQUARE : SRC_PLAIN;
+    src.x = x;
+    src.is_center = nullptr;
+    src.max_finite_bits = nullptr;
+    src.p_out = nullptr;
+    float* total = vals + plan[1] + plan[2];
+    rc = run_pairwise(src, plan_dev, plan[1], vals, total, st);
+    if (rc) return rc;
+    CU_TRY(cudaMemcpyAsync(out_host, total, 4, cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    return 0;
+}
