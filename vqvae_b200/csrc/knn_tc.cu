@@ -129,6 +129,11 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
+__device__ __forceinline__ float fmin3(float a, float b, float c) {  // FMNMX3 on sm_100a
+    float r;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // byte offset of element (row r, float k) inside a 128-row operand tile image
@@ -369,14 +374,15 @@ __global__ void __launch_bounds__(C::kThreads, 1) knn_filter_tc_kernel(const flo
                 tmem_ld_wait();
 #pragma unroll
                 for (int part = 0; part < kGroup; ++part) {
-                    float t[16];
+                    // minimum of each 8-column octet with three-input minima (FMNMX3: 4 per octet), then of the part
+                    float g8[4];
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) t[i] = fminf(v[part][i], v[part][i + 16]);
-#pragma unroll
-                    for (int w = 8; w; w >>= 1)
-#pragma unroll
-                        for (int i = 0; i < w; ++i) t[i] = fminf(t[i], t[i + w]);
-                    if (__any_sync(0xffffffffu, t[0] < thr)) {
+                    for (int o = 0; o < 4; ++o) {
+                        const float* u = &v[part][8 * o];
+                        g8[o] = fminf(fmin3(u[0], u[1], u[2]), fmin3(fmin3(u[3], u[4], u[5]), u[6], u[7]));
+                    }
+                    const float tmin = fminf(fmin3(g8[0], g8[1], g8[2]), g8[3]);
+                    if (__any_sync(0xffffffffu, tmin < thr)) {
                         if (ES > 1) {  // the partner warp shares these rows' lists: take the block's lock, refresh thr
                             if (lane == 0)
                                 while (atomicCAS(lock, 0, 1) != 0) {
@@ -387,10 +393,14 @@ __global__ void __launch_bounds__(C::kThreads, 1) knn_filter_tc_kernel(const flo
                         }
                         const float thr_before = thr;
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            const bool pend = v[part][i] < thr;
-                            if (__any_sync(0xffffffffu, pend))
-                                thr = coop_insert(sc, ix, row0w, pend, v[part][i], c0 + (q4 * kGroup + part) * 32 + i, thr);
+                        for (int o = 0; o < 4; ++o) {
+                            if (!__any_sync(0xffffffffu, g8[o] < thr)) continue;  // (thr only ever drops: still exact)
+#pragma unroll
+                            for (int i = 8 * o; i < 8 * o + 8; ++i) {
+                                const bool pend = v[part][i] < thr;
+                                if (__any_sync(0xffffffffu, pend))
+                                    thr = coop_insert(sc, ix, row0w, pend, v[part][i], c0 + (q4 * kGroup + part) * 32 + i, thr);
+                            }
                         }
                         if (thr != thr_before) thr_s[row] = thr;  // publish: final write-out and (ES > 1) the partner
                         if (ES > 1) {
