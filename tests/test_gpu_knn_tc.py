@@ -33,6 +33,27 @@ def test_knn_tc_dims_vs_sklearn(dg, d, n, k):
     assert np.array_equal(idx2.cpu().numpy(), iref[1000:1777])
 
 
+@pytest.mark.parametrize("env", [{"GEOCB_KNN_TC_PAIR": "0"}, {"GEOCB_KNN_TC_N": "256"}, {"GEOCB_KNN_TC_ES": "2"}],
+                         ids=["two_tile_cta", "n256", "es2"])
+def test_knn_tc_d16_other_configurations(dg, env, monkeypatch):
+    """d <= 16 runs one A tile per CTA and two CTAs per SM by default; the other kernel configurations (two-tile CTA,
+    N = 256 MMAs, two epilogue warps per row block) stay selectable and must give the same lists."""
+    from sklearn.neighbors import NearestNeighbors
+    z = np.random.RandomState(5).randn(7000, 16).astype(np.float32)
+    z[100:140] = z[60:100]  # duplicates: ties broken by index
+    zt = torch.from_numpy(z).cuda()
+    idx0, dist0, _ = dg.knn_topk(zt, 21)
+    for k_, v_ in env.items():
+        monkeypatch.setenv(k_, v_)
+    idx1, dist1, _ = dg.knn_topk(zt, 21)
+    assert torch.equal(idx0, idx1) and torch.equal(dist0, dist1)
+    dref, iref = NearestNeighbors(n_neighbors=21, algorithm="brute").fit(z).kneighbors(z)
+    np.testing.assert_allclose(dist0.cpu().numpy(), dref, rtol=2e-6, atol=1e-6)
+    # (twins tie: sklearn may list them in either order, ours lists the lower index first)
+    assert np.array_equal(np.sort(idx0.cpu().numpy()[:, :20], axis=1), np.sort(iref[:, :20], axis=1)) or \
+        (np.sort(idx0.cpu().numpy(), axis=1) == np.sort(iref, axis=1)).all(axis=1).mean() > 0.995
+
+
 @pytest.mark.parametrize("d,K", [(16, 512), (32, 512), (64, 1024), (128, 64)])
 def test_nearest_medoid_assign(dg, d, K):
     """Downstream assignment of held-out latents (src/eval/evaluate_codebook_health.py:13-26): the code is the exactly

@@ -51,6 +51,9 @@ struct Cfg {
     static constexpr int NBUF = 512 / (ATILES * NB);     // accumulator buffers per A tile that fit the 512 TMEM columns
     static_assert(NBUF == 1 || NBUF == 2 || NBUF == 4, "TMEM budget");
     static constexpr int kBufs = NBUF > 2 ? 2 : NBUF;
+    static constexpr int kTmemCols = kBufs * ATILES * NB;  // 512, or 256 for the one-tile configurations
+    // one-tile CTAs at d <= 16 are small enough (95 KB of shared memory, 256 TMEM columns) to run two per SM
+    static constexpr int kMinCtas = (ATILES == 1 && DP == 16) ? 2 : 1;
     // D=f32, A=B=tf32, K-major both, M=128, N=NB
     static constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NB >> 3) << 17) | ((128u >> 4) << 24);
 };
@@ -243,6 +246,19 @@ __device__ __noinline__ float coop_insert(float* sc, int32_t* ix, int row0w, boo
     return thr;
 }
 
+#ifdef GEOCB_KNN_TRACE  // profiling builds only (`make knntrace`, tools/prof_knn_trace.py): clocks per phase, summed per warp
+__device__ unsigned long long g_knn_trace[16];
+#define KT_NOW() clock64()
+#define KT_DECL() unsigned long long kt_acc[16] = {0}
+#define KT_ADD(slot, dt) kt_acc[slot] += (unsigned long long)(dt)
+#define KT_FLUSH() do { if ((threadIdx.x & 31) == 0) for (int kt_i = 0; kt_i < 16; ++kt_i) if (kt_acc[kt_i]) atomicAdd(&g_knn_trace[kt_i], kt_acc[kt_i]); } while (0)
+#else
+#define KT_NOW() 0LL
+#define KT_DECL() do { } while (0)
+#define KT_ADD(slot, dt) do { } while (0)
+#define KT_FLUSH() do { } while (0)
+#endif
+
 template <int STAGES>
 struct alignas(8) TcBars {
     uint64_t a_full, full[STAGES], empty[STAGES], tmem_full[4], tmem_empty[4];  // accumulator barriers: [buffer][A tile]
@@ -251,7 +267,7 @@ struct alignas(8) TcBars {
 };
 
 template <class C>
-__global__ void __launch_bounds__(C::kThreads, 1) knn_filter_tc_kernel(const float* __restrict__ aimg,
+__global__ void __launch_bounds__(C::kThreads, C::kMinCtas) knn_filter_tc_kernel(const float* __restrict__ aimg,
                                                                         const float* __restrict__ bimg, int64_t Mp,
                                                                         int64_t nq, int32_t* cand_idx, float* cand_thr) {
     constexpr int kTileBytes = C::kTileBytes, kStages = C::STAGES, kRowsPerCta = C::kRowsPerCta, NSUB = C::NSUB;
@@ -281,8 +297,9 @@ __global__ void __launch_bounds__(C::kThreads, 1) knn_filter_tc_kernel(const flo
         ix[i] = -1;
     }
     for (int i = tid; i < kRowsPerCta; i += C::kThreads) thr_s[i] = __uint_as_float(F32_INF_BITS);
-    if (warp == kIssuer) {  // one warp allocates all 512 TMEM columns (1 CTA per SM: the shared-memory footprint forces it)
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&bars->tmem_base))
+    if (warp == kIssuer) {  // one warp allocates the CTA's TMEM columns (all 512, or 256 when two CTAs share the SM)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&bars->tmem_base)),
+                     "n"(C::kTmemCols)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -290,6 +307,8 @@ __global__ void __launch_bounds__(C::kThreads, 1) knn_filter_tc_kernel(const flo
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *(volatile uint32_t*)&bars->tmem_base;
+    KT_DECL();  // [0] epilogue: wait for the accumulator [2] TMEM loads [3] screen + insert [5] warp-chunks;
+                // [8] issuer: wait B stage [9] wait accumulators drained [10] issue + [9] [11] chunks
 
     if (warp == kProducer) {
         // ===== TMA producer: A tiles once, then the ring of B (sub-)tiles =====
@@ -322,15 +341,20 @@ __global__ void __launch_bounds__(C::kThreads, 1) knn_filter_tc_kernel(const flo
                 for (int sub = 0; sub < NSUB; ++sub) {
                     const int64_t it = c * NSUB + sub;
                     const int st = (int)(it % kStages);
+                    const long long ki0 = KT_NOW();
                     mbar_wait(&bars->full[st], (uint32_t)((it / kStages) & 1));
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const long long ki1 = KT_NOW();
+                    KT_ADD(8, ki1 - ki0);
                     const int t0 = sub == 0 ? 0 : kHiSteps, t1 = (NSUB == 1 || sub == 1) ? C::kSteps : kHiSteps;
                     const int kg0 = sub == 0 ? 0 : C::kSplit;
 #pragma unroll
                     for (int a = 0; a < AT; ++a) {
                         if (sub == 0) {  // the epilogue must have drained this accumulator
+                            const long long kw = KT_NOW();
                             mbar_wait(&bars->tmem_empty[buf * AT + a], (use & 1) ^ 1);
                             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                            KT_ADD(9, KT_NOW() - kw);
                         }
                         const uint32_t d_tmem = tmem_base + (uint32_t)((buf * AT + a) * NB);
 #pragma unroll
@@ -344,6 +368,8 @@ __global__ void __launch_bounds__(C::kThreads, 1) knn_filter_tc_kernel(const flo
                         if (NSUB == 1 || sub == 1) umma_commit(&bars->tmem_full[buf * AT + a]);  // this accumulator is complete
                     }
                     umma_commit(&bars->empty[st]);  // smem stage reusable once these MMAs have read it
+                    KT_ADD(10, KT_NOW() - ki1);
+                    KT_ADD(11, 1);
                 }
             }
         }
@@ -359,8 +385,11 @@ __global__ void __launch_bounds__(C::kThreads, 1) knn_filter_tc_kernel(const flo
         float thr = __uint_as_float(F32_INF_BITS);
         for (int64_t c = 0; c < nchunks; ++c) {
             const int buf = (int)(c % kBufs);
+            const long long kt0 = KT_NOW();
             mbar_wait(&bars->tmem_full[buf * AT + a], (uint32_t)((c / kBufs) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            KT_ADD(0, KT_NOW() - kt0);
+            KT_ADD(5, 1);
             const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((buf * AT + a) * NB + h * kCols);
             const int32_t c0 = (int32_t)(c * NB + h * kCols);
             if (ES > 1) thr = fminf(thr, *(volatile float*)&thr_s[row]);  // the partner warp may have tightened it
@@ -369,9 +398,12 @@ __global__ void __launch_bounds__(C::kThreads, 1) knn_filter_tc_kernel(const flo
                 // screen with the values kept in registers: kGroup 32-column loads in flight, one wait, min-trees; a hit
                 // part is searched with one warp vote per column and every survivor is inserted by the whole warp
                 float v[kGroup][32];
+                const long long kt1 = KT_NOW();
 #pragma unroll
                 for (int part = 0; part < kGroup; ++part) tmem_ld32(taddr + (q4 * kGroup + part) * 32, v[part]);
                 tmem_ld_wait();
+                const long long kt2 = KT_NOW();
+                KT_ADD(2, kt2 - kt1);
 #pragma unroll
                 for (int part = 0; part < kGroup; ++part) {
                     // minimum of each 8-column octet with three-input minima (FMNMX3: 4 per octet), then of the part
@@ -410,12 +442,14 @@ __global__ void __launch_bounds__(C::kThreads, 1) knn_filter_tc_kernel(const flo
                         }
                     }
                 }
+                KT_ADD(3, KT_NOW() - kt2);
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
             if (lane == 0) mbar_arrive(&bars->tmem_empty[buf * AT + a]);
         }
     }
+    KT_FLUSH();
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (tid < kRowsPerCta) {  // every epilogue warp is done: thread = row writes its list out
@@ -426,7 +460,7 @@ __global__ void __launch_bounds__(C::kThreads, 1) knn_filter_tc_kernel(const flo
         }
     }
     if (warp == kIssuer) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::kTmemCols) : "memory");
     }
 }
 
@@ -448,6 +482,7 @@ int launch_tc(const float* z, const float* zq, int64_t M, int d, int64_t nq, flo
 }
 
 typedef Cfg<16, 2, 4, 1, 128, 1> Cfg16;    // N = 128 MMAs, two accumulator buffers per A tile, 8 epilogue warps
+typedef Cfg<16, 1, 2, 1, 128, 1> Cfg16P;   // one A tile per CTA, TWO CTAs per SM: each CTA's MMAs fill the other's epilogue stalls
 typedef Cfg<16, 2, 4, 1, 128, 2> Cfg16E2;  // the same with 16 epilogue warps: two per 32-row block, 64 columns each
 typedef Cfg<16, 2, 3, 1, 256, 1> Cfg16W;   // N = 256 MMAs (half as many instructions), one buffer per A tile
 typedef Cfg<32, 2, 2, 1, 128, 1> Cfg32;
@@ -474,6 +509,14 @@ int knn_filter_tc(const float* z, const float* zq, int64_t M, int d, int64_t nq,
         case 16: {
             // N of the tcgen05.mma instructions at d <= 16: 128 (default) | 256.  Measured equal at C2 (2.44 vs 2.50 s): the
             // filter is bound by the tensor pipe's sustained tf32 rate, not by instruction count
+            // Default: one A tile per CTA and two CTAs per SM.  The phase clocks (tools/prof_knn_trace.py,
+            // profiles/r2_knn_phase_clocks.txt) show the two-tile CTA fully serialised: its issuer spends 1058 clocks per
+            // chunk issuing 14 MMAs at the tensor pipe's tf32 rate, then waits for the slowest of 8 epilogue warps, which
+            // in turn wait for the MMAs (56 % of their time).  Two independent CTAs fill each other's gaps: tensor pipe
+            // 91 % busy, 1.75 s against 1.89 s at C2.  GEOCB_KNN_TC_PAIR=0 selects the two-tile CTA.
+            const char* pp = getenv("GEOCB_KNN_TC_PAIR");
+            if (!(pp && atoi(pp) == 0) && !getenv("GEOCB_KNN_TC_N") && !getenv("GEOCB_KNN_TC_ES"))
+                return launch_tc<Cfg16P>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
             const char* e = getenv("GEOCB_KNN_TC_N");
             if (e && atoi(e) == 256) return launch_tc<Cfg16W>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
             // epilogue warps per 32-row block: GEOCB_KNN_TC_ES=2 splits each block's columns over two warps that share the
@@ -486,3 +529,14 @@ int knn_filter_tc(const float* z, const float* zq, int64_t M, int d, int64_t nq,
         default: return launch_tc<Cfg64>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
     }
 }
+
+#ifdef GEOCB_KNN_TRACE
+extern "C" __attribute__((visibility("default"))) int geocb_knn_trace_read(unsigned long long* out16, int reset) {
+    if (cudaMemcpyFromSymbol(out16, g_knn_trace, sizeof(g_knn_trace)) != cudaSuccess) return -1;
+    if (reset) {
+        unsigned long long z[16] = {0};
+        if (cudaMemcpyToSymbol(g_knn_trace, z, sizeof(z)) != cudaSuccess) return -1;
+    }
+    return 0;
+}
+#endif
