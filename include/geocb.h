@@ -37,8 +37,9 @@ int geocb_device_info(int* sm_count, int* cc);
  * For query rows [q_lo,q_hi) of z[M,d] (row-major f32) find the kq nearest rows
  * of z (self included), ordered by (exact fp64 squared distance, index).
  *   pass 1: filter  |b|^2 - 2ab  over all candidates, keeping the best kq+slack per row:
- *           d <= 64 and kq <= 26: tcgen05 tensor cores, 3xTF32 split (fp32-grade scores,
- *           csrc/knn_tc.cu; env GEOCB_KNN_TC=0 disables); otherwise fused fp32 FFMA2 tiles (d <= 64, kq <= 56)
+ *           d <= 64 and kq <= 26: tcgen05 tensor cores, operands split into bf16 (default) or tf32
+ *           hi + lo pieces (fp32-grade scores, csrc/knn_tc.cu; env GEOCB_KNN_TC_FMT=tf32 selects the tf32
+ *           pieces, GEOCB_KNN_TC=0 disables the tensor-core filter); otherwise fused fp32 FFMA2 tiles (d <= 64, kq <= 56)
  *           or, beyond that, the exact fp64 kernel for every row.
  *   pass 2: exact fp64 re-rank of the candidates; rows whose filter margin is
  *           not provably safe are redone by an exact fp64 brute-force kernel.

@@ -33,11 +33,14 @@ def test_knn_tc_dims_vs_sklearn(dg, d, n, k):
     assert np.array_equal(idx2.cpu().numpy(), iref[1000:1777])
 
 
-@pytest.mark.parametrize("env", [{"GEOCB_KNN_TC_PAIR": "0"}, {"GEOCB_KNN_TC_N": "256"}, {"GEOCB_KNN_TC_ES": "2"}],
-                         ids=["two_tile_cta", "n256", "es2"])
+@pytest.mark.parametrize("env", [{"GEOCB_KNN_TC_FMT": "tf32"}, {"GEOCB_KNN_TC_FMT": "tf32", "GEOCB_KNN_TC_PAIR": "0"},
+                                 {"GEOCB_KNN_TC_FMT": "tf32", "GEOCB_KNN_TC_N": "256"},
+                                 {"GEOCB_KNN_TC_FMT": "tf32", "GEOCB_KNN_TC_ES": "2"}, {"GEOCB_KNN_TC_N": "64"}],
+                         ids=["tf32_pair", "tf32_two_tile_cta", "tf32_n256", "tf32_es2", "bf16_n64"])
 def test_knn_tc_d16_other_configurations(dg, env, monkeypatch):
-    """d <= 16 runs one A tile per CTA and two CTAs per SM by default; the other kernel configurations (two-tile CTA,
-    N = 256 MMAs, two epilogue warps per row block) stay selectable and must give the same lists."""
+    """d <= 16 runs bf16-split operands, one A tile per CTA and two CTAs per SM by default; the other kernel
+    configurations (tf32-split operands with one- or two-tile CTAs, N = 256 MMAs, two epilogue warps per row block; bf16
+    with 64-candidate chunks) stay selectable and must give the same lists."""
     from sklearn.neighbors import NearestNeighbors
     z = np.random.RandomState(5).randn(7000, 16).astype(np.float32)
     z[100:140] = z[60:100]  # duplicates: ties broken by index
@@ -52,6 +55,17 @@ def test_knn_tc_d16_other_configurations(dg, env, monkeypatch):
     # (twins tie: sklearn may list them in either order, ours lists the lower index first)
     assert np.array_equal(np.sort(idx0.cpu().numpy()[:, :20], axis=1), np.sort(iref[:, :20], axis=1)) or \
         (np.sort(idx0.cpu().numpy(), axis=1) == np.sort(iref, axis=1)).all(axis=1).mean() > 0.995
+
+
+def test_knn_tc_tf32_format_other_dims(dg, monkeypatch):
+    """d = 32 / 64 with the tf32-split operand format (GEOCB_KNN_TC_FMT=tf32; bf16 is the default everywhere)."""
+    for d in (32, 64):
+        z = torch.from_numpy(np.random.RandomState(d).randn(4000, d).astype(np.float32)).cuda()
+        monkeypatch.delenv("GEOCB_KNN_TC_FMT", raising=False)
+        idx0, dist0, _ = dg.knn_topk(z, 21)
+        monkeypatch.setenv("GEOCB_KNN_TC_FMT", "tf32")
+        idx1, dist1, _ = dg.knn_topk(z, 21)
+        assert torch.equal(idx0, idx1) and torch.equal(dist0, dist1)
 
 
 @pytest.mark.parametrize("d,K", [(16, 512), (32, 512), (64, 1024), (128, 64)])

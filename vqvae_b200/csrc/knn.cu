@@ -417,7 +417,7 @@ static int knn_query_impl(const float* z, const float* zq, int64_t M, int d, int
         if ((rc = knn_filter_tc(z, zq, M, d, nq, bimg, aimg, max_nrm, cand_idx, cand_thr, st))) return rc;
         const unsigned rb = (unsigned)((nq * 32 + 255) / 256);
         knn_rerank_kernel<32><<<rb, 256, 0, st>>>(z, zq, M, d, nq, kq, cand_idx, cand_thr, max_nrm,
-                                                   7.62939453125e-06 /* 2^-17 */, out_idx, out_dist, unsafe_rows,
+                                                   knn_tc_eps_unit(), out_idx, out_dist, unsafe_rows,
                                                    unsafe_cnt);
         KERNEL_CHECK();
         knn_exact_kernel<<<di.sm_count * 4, 256, 0, st>>>(z, zq, M, d, kq, unsafe_rows, unsafe_cnt, 0, out_idx,

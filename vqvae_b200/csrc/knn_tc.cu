@@ -3,29 +3,36 @@
 // Replaces pass 1 of knn.cu (the fp32 FFMA2 filter) for the reference's kNN query
 // (src/geo/knn_graph_optimized.py:39-42).  Only the contraction runs on tensor cores:
 //     score(q,c) = |c|^2 - 2 q.c      (|q|^2 is constant per row and dropped)
-// is one tf32 GEMM with fp32-grade accuracy by splitting every operand into tf32 hi + lo parts
-// (hi*hi + lo*hi + hi*lo, the lo*lo term is below 2^-22) and folding |c|^2 in as one more K-step:
-//     A row (query)     = [ -2a_hi (16) | -2a_lo (16) | 1 1 0 0 0 0 0 0 ]      40 floats
-//     B row (candidate) = [   b_hi (16) |   b_lo (16) | n_hi n_lo 0 0 0 0 0 0 ]
-//     7 MMAs of K=8 per tile:  hi.hi (2)  lo.hi (2)  hi.lo (2)  ones.norm (1)
+// is one tensor-core GEMM with fp32-grade accuracy by splitting every operand into hi + lo pieces
+// (hi*hi + lo*hi + hi*lo; the lo*lo term is dropped) and folding |c|^2 in as one more K-step.  Two operand formats:
+//   bf16 pieces (default; kind::f16 MMAs of K = 16, twice the tf32 rate), DP = 16:
+//     A row (query)     = [ -2a_hi (16) | -2a_lo (16) | 1 1 1 0 ... ]            48 bf16 = 6 K-groups of 16 bytes
+//     B row (candidate) = [   b_hi (16) |   b_lo (16) | n_0 n_1 n_2 0 ... ]      (|c|^2 in three bf16 pieces: 2^-24)
+//     4 MMAs per tile and chunk:  hi.hi  lo.hi  hi.lo  ones.norm         error <= 2^-14 (|b|^2 + 2|a||b|)
+//   tf32 pieces (GEOCB_KNN_TC_FMT=tf32; kind::tf32 MMAs of K = 8), DP = 16:
+//     A row = [ -2a_hi (16) | -2a_lo (16) | 1 1 0 0 0 0 0 0 ],  B row = [ b_hi | b_lo | n_hi n_lo 0 ... ]   40 floats
+//     7 MMAs per tile and chunk:  hi.hi (2)  lo.hi (2)  hi.lo (2)  ones.norm (1)     error <= 2^-17 (...)
+// The error bound only sets the margin of the exact re-rank's certificate (knn.cu): results never depend on the format.
 // Operand tiles are stored in global memory already in the UMMA canonical K-major no-swizzle image
-// (8x16-byte core matrices; LBO = 128 rows * 16 B between K-groups, SBO = 128 B between 8-row groups),
-// so one 1-D TMA bulk copy (cp.async.bulk + mbarrier) stages a 128-candidate tile (20 KB).
-// One CTA owns 256 query rows = two 128-row A tiles, so each staged B tile feeds two accumulators
-// (halves the L2->SM operand traffic); accumulators are double-buffered in TMEM (4 x 128 columns = all 512).
-//   warp 8  lane 0 : TMA producer (A tiles once, then the B tile ring)
-//   warp 9  lane 0 : tcgen05.mma issuer; tcgen05.commit releases smem stages / publishes accumulators
-//   warps 0-7      : epilogue -- thread = query row: tcgen05.ld 32 scores at a time, a min-tree screens them
-//                    against the row's current threshold, the rare survivors enter the row's L-entry list.
+// (8x16-byte core matrices; LBO = rows * 16 B between K-groups, SBO = 128 B between 8-row groups),
+// so one 1-D TMA bulk copy (cp.async.bulk + mbarrier) stages a 128-candidate tile.
+// CTA shapes (Cfg): one 128-row A tile per CTA and TWO CTAs per SM where shared memory and 256 TMEM columns allow it
+// (bf16 DP <= 32, tf32 DP = 16: two independent pipelines fill each other's stalls), else 256 rows = two A tiles that
+// share every staged B tile.  Accumulators are double-buffered in TMEM.
+//   warp E   lane 0 : TMA producer (A tiles once, then the B tile ring)          (E = number of epilogue warps: 4 or 8)
+//   warp E+1 lane 0 : tcgen05.mma issuer; tcgen05.commit releases smem stages / publishes accumulators
+//   warps 0..E-1    : epilogue -- thread = query row: tcgen05.ld 32 scores at a time, a min-tree (FMNMX3) screens them
+//                     against the row's current threshold, the rare survivors enter the row's L-entry list.
 // Output is the same (cand_idx, cand_thr) pair knn.cu's exact fp64 re-rank + certificate consume.
-//
-// The row image scales with the padded dimension DP in {16, 32, 64}: [hi DP | lo DP | norm/ones 8] floats, 3*DP/8 + 1
-// MMAs per tile pair (7 / 13 / 25).  Shared memory decides the shape: DP=16: two A tiles, 4 B stages; DP=32: two A
-// tiles, 2 stages; DP=64: ONE A tile (68 KB) and the B tile staged in two K-halves (hi | lo+norm, 3 half stages).
+// Measured phase by phase with `make knntrace` + tools/prof_knn_trace.py (profiles/r2_knn_phase_clocks.txt).
 #include <stdlib.h>
 #include "common.cuh"
 #include "knn_tc.cuh"
 
+
+#ifndef KNN_TC_DEFAULT_BF16
+#define KNN_TC_DEFAULT_BF16 1
+#endif
 
 namespace {
 
@@ -33,29 +40,35 @@ constexpr int kTileRows = 128;
 constexpr int kLBO = kTileRows * 16;        // bytes between K-groups
 constexpr int kL = 32;                      // list length (kq <= 26)
 
-template <int DP_, int ATILES_, int STAGES_, int NSUB_, int NB_, int ES_>
+// BF = 0: operands split into tf32 hi + lo, 4 values per 16-byte K-group, MMAs of K = 8 (kind::tf32);
+// BF = 1: operands split into bf16 hi + lo, 8 values per K-group, MMAs of K = 16 (kind::f16) at twice the tensor rate.
+template <int DP_, int ATILES_, int STAGES_, int NSUB_, int NB_, int ES_, int BF_ = 0>
 struct Cfg {
-    static constexpr int DP = DP_, ATILES = ATILES_, STAGES = STAGES_, NSUB = NSUB_, NB = NB_, ES = ES_;
+    static constexpr int DP = DP_, ATILES = ATILES_, STAGES = STAGES_, NSUB = NSUB_, NB = NB_, ES = ES_, BF = BF_;
+    static constexpr int kHiGroups = BF ? DP / 8 : DP / 4;  // K-groups of the hi part (= of the lo part)
     // ES epilogue warps share each 32-row block (each takes NB/ES of a chunk's columns)
     static constexpr int kEpiWarps = 4 * ATILES * ES, kThreads = (kEpiWarps + 2) * 32;
-    static constexpr int kRowFloats = 2 * DP + 8;        // floats per operand row image
-    static constexpr int kKGroups = kRowFloats / 4;      // 16-byte K-groups per row
-    static constexpr int kTileBytes = kKGroups * kLBO;   // A tile (128 rows): 20480 / 36864 / 69632
+    static constexpr int kKGroups = 2 * kHiGroups + 2;   // 16-byte K-groups per row: hi | lo | norm / ones (one MMA step)
+    static constexpr int kTileBytes = kKGroups * kLBO;   // A tile (128 rows): tf32 20480 / 36864 / 69632, bf16 12288 / 20480 / 36864
     static constexpr int kLboB = NB * 16;                // candidate (B) tiles hold NB = 128 or 256 rows: N of the MMA
     static constexpr int kTileBytesB = kKGroups * kLboB;
     static constexpr int kRowsPerCta = ATILES * kTileRows;
     // B sub-tiles (K-group ranges): one, or [hi) and [lo + norm)
-    static constexpr int kSplit = NSUB == 1 ? kKGroups : DP / 4;
-    static constexpr int kStageBytes = (NSUB == 1 ? kKGroups : (kKGroups - DP / 4)) * kLboB;
-    static constexpr int kSteps = 3 * DP / 8 + 1;
+    static constexpr int kSplit = NSUB == 1 ? kKGroups : kHiGroups;
+    static constexpr int kStageBytes = (NSUB == 1 ? kKGroups : (kKGroups - kHiGroups)) * kLboB;
+    static constexpr int kChunks = kHiGroups / 2;        // MMA-K sized pieces of the hi part (an MMA reads two K-groups)
+    static constexpr int kSteps = 3 * kChunks + 1;       // hi.hi, lo.hi, hi.lo per piece + ones.norm
     static constexpr int NBUF = 512 / (ATILES * NB);     // accumulator buffers per A tile that fit the 512 TMEM columns
-    static_assert(NBUF == 1 || NBUF == 2 || NBUF == 4, "TMEM budget");
+    static_assert(NBUF == 1 || NBUF == 2 || NBUF == 4 || NBUF == 8, "TMEM budget");
     static constexpr int kBufs = NBUF > 2 ? 2 : NBUF;
     static constexpr int kTmemCols = kBufs * ATILES * NB;  // 512, or 256 for the one-tile configurations
-    // one-tile CTAs at d <= 16 are small enough (95 KB of shared memory, 256 TMEM columns) to run two per SM
-    static constexpr int kMinCtas = (ATILES == 1 && DP == 16) ? 2 : 1;
-    // D=f32, A=B=tf32, K-major both, M=128, N=NB
-    static constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NB >> 3) << 17) | ((128u >> 4) << 24);
+    // one-tile CTAs whose shared memory fits twice (and 256 TMEM columns each) run two per SM
+    static constexpr int kSmemEstimate = ATILES * kTileBytes + STAGES * kStageBytes + kL * kRowsPerCta * 8 + 2048;
+    static constexpr int kBySmem = (225 * 1024) / kSmemEstimate, kByTmem = 512 / kTmemCols;
+    static constexpr int kMinCtas = ATILES != 1 ? 1 : (kBySmem < kByTmem ? (kBySmem < 1 ? 1 : kBySmem) : kByTmem);
+    // D=f32, A=B=tf32 (2) or bf16 (1), K-major both, M=128, N=NB  (cute::UMMA::InstrDescriptor)
+    static constexpr uint32_t kFmt = BF ? 1u : 2u;
+    static constexpr uint32_t kIdesc = (1u << 4) | (kFmt << 7) | (kFmt << 10) | ((uint32_t)(NB >> 3) << 17) | ((128u >> 4) << 24);
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -102,15 +115,27 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo) 
            (1ULL << 46);
 }
 // (instruction descriptor, cute::UMMA::InstrDescriptor layout: Cfg::kIdesc)
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
-        "}\n" ::"r"(tmem_d),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
+template <int BF>
+__device__ __forceinline__ void umma_issue(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    if constexpr (BF) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "setp.ne.b32 p, %4, 0;\n"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+            "}\n" ::"r"(tmem_d),
+            "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+            : "memory");
+    } else {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "setp.ne.b32 p, %4, 0;\n"
+            "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+            "}\n" ::"r"(tmem_d),
+            "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+            : "memory");
+    }
 }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
@@ -143,19 +168,19 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 __device__ __forceinline__ int img_off(int r, int k, int lbo) { return (k >> 2) * lbo + (r >> 3) * 128 + (r & 7) * 16 + (k & 3) * 4; }
 // K-group pairs (A kg, B kg) of MMA step t for padded dimension DP: steps are grouped by the B sub-tile they read:
 // first every step on B's hi part (hi.hi and lo.hi per 8-float chunk), then hi.lo per chunk, then ones.norm.
-template <int DP>
+template <int H>  // H = K-groups of the hi part
 __device__ __forceinline__ void mma_step(int t, int& akg, int& bkg) {
-    constexpr int C = DP / 8;
+    constexpr int C = H / 2;
     if (t < 2 * C) {
         const int j = t >> 1;
-        akg = (t & 1) ? DP / 4 + 2 * j : 2 * j;
+        akg = (t & 1) ? H + 2 * j : 2 * j;
         bkg = 2 * j;
     } else if (t < 3 * C) {
         const int j = t - 2 * C;
         akg = 2 * j;
-        bkg = DP / 4 + 2 * j;
+        bkg = H + 2 * j;
     } else {
-        akg = bkg = DP / 2;
+        akg = bkg = 2 * H;
     }
 }
 
@@ -206,6 +231,61 @@ __global__ void knn_tc_prep_kernel(const float* __restrict__ z, const float* __r
     const int r = (int)((is_b ? row : qrow) % tile_rows);
     float* base = (is_b ? bimg : aimg) + tile * ((int64_t)kgroups * tile_rows * 4);
     *(float4*)((char*)base + img_off(r, kg * 4, tile_rows * 16)) = make_float4(out[0], out[1], out[2], out[3]);
+}
+
+// bf16 operand images (Cfg<..., BF = 1>): K-groups of 8 bf16: hi | lo | norm.  x = hi + lo + r with |r| <= 2^-16 |x|
+// (two round-to-nearest 8-bit pieces); |c|^2 goes in as three bf16 pieces (2^-24) against three ones.
+__device__ __forceinline__ uint32_t bf16_bits(float x) {
+    uint16_t r;
+    asm("cvt.rn.bf16.f32 %0, %1;" : "=h"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float bf16_val(uint32_t b) { return __uint_as_float(b << 16); }
+__global__ void knn_tc_prep_bf16_kernel(const float* __restrict__ z, const float* __restrict__ zq, int64_t M, int d, int dp,
+                                        int nb, int64_t Mp, int64_t nq, int64_t nq_pad, float* bimg, float* aimg,
+                                        unsigned int* max_nrm_bits) {
+    const int hi_groups = dp / 8, kgroups = 2 * hi_groups + 2;
+    const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t row = gid / kgroups;
+    const int kg = (int)(gid % kgroups);
+    const bool is_b = row < Mp;
+    const int64_t qrow = row - Mp;
+    if (!is_b && qrow >= nq_pad) return;
+    const bool live = is_b ? row < M : qrow < nq;
+    const float* src = is_b ? z + row * d : zq + qrow * d;
+    uint32_t h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (kg < 2 * hi_groups) {
+        const int c0 = (kg % hi_groups) * 8;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            float v = (live && c0 + i < d) ? src[c0 + i] : 0.f;
+            if (!is_b) v *= -2.0f;
+            const uint32_t hi = bf16_bits(v);
+            h[i] = kg < hi_groups ? hi : bf16_bits(v - bf16_val(hi));
+        }
+    } else if (kg == 2 * hi_groups) {
+        if (is_b) {
+            float s = 0.f;
+            if (live) {
+                for (int i = 0; i < d; ++i) s = __fmaf_rn(src[i], src[i], s);
+                atomicMax(max_nrm_bits, __float_as_uint(s));
+                h[0] = bf16_bits(s);
+                const float r1 = s - bf16_val(h[0]);
+                h[1] = bf16_bits(r1);
+                h[2] = bf16_bits(r1 - bf16_val(h[1]));
+            } else {
+                h[0] = bf16_bits(3.0e38f);  // pad candidates: never kept
+            }
+        } else {
+            h[0] = h[1] = h[2] = 0x3F80u;  // 1.0
+        }
+    }
+    const int tile_rows = is_b ? nb : kTileRows;
+    const int64_t tile = (is_b ? row : qrow) / tile_rows;
+    const int r = (int)((is_b ? row : qrow) % tile_rows);
+    float* base = (is_b ? bimg : aimg) + tile * ((int64_t)kgroups * tile_rows * 4);
+    *(uint4*)((char*)base + img_off(r, kg * 4, tile_rows * 16)) =
+        make_uint4(h[0] | (h[1] << 16), h[2] | (h[3] << 16), h[4] | (h[5] << 16), h[6] | (h[7] << 16));
 }
 
 // ------------------------------------------------------------------ filter ----
@@ -333,7 +413,7 @@ __global__ void __launch_bounds__(C::kThreads, C::kMinCtas) knn_filter_tc_kernel
         if (lane == 0) {
             mbar_wait(&bars->a_full, 0);
             const uint32_t a_addr = smem_u32(a_s), b_addr = smem_u32(b_s);
-            constexpr int kHiSteps = NSUB == 1 ? C::kSteps : 2 * (C::DP / 8);  // steps that read B sub-tile 0
+            constexpr int kHiSteps = NSUB == 1 ? C::kSteps : 2 * C::kChunks;  // steps that read B sub-tile 0
             for (int64_t c = 0; c < nchunks; ++c) {
                 const int buf = (int)(c % kBufs);
                 const uint32_t use = (uint32_t)(c / kBufs);  // how often this buffer has been used before
@@ -360,8 +440,8 @@ __global__ void __launch_bounds__(C::kThreads, C::kMinCtas) knn_filter_tc_kernel
 #pragma unroll
                         for (int t = t0; t < t1; ++t) {
                             int akg, bkg;
-                            mma_step<C::DP>(t, akg, bkg);
-                            umma_tf32(d_tmem, umma_desc(a_addr + a * kTileBytes + akg * kLBO, kLBO),
+                            mma_step<C::kHiGroups>(t, akg, bkg);
+                            umma_issue<C::BF>(d_tmem, umma_desc(a_addr + a * kTileBytes + akg * kLBO, kLBO),
                                       umma_desc(b_addr + st * C::kStageBytes + (bkg - kg0) * C::kLboB, C::kLboB), C::kIdesc,
                                       t > 0 ? 1u : 0u);
                         }
@@ -469,8 +549,12 @@ int launch_tc(const float* z, const float* zq, int64_t M, int d, int64_t nq, flo
               unsigned int* max_nrm_bits, int32_t* cand_idx, float* cand_thr, cudaStream_t st) {
     const int64_t Mp = align_up(M, 256), nqp = align_up(nq, C::kRowsPerCta);  // (256: every config's B tile divides it)
     const int64_t threads = (Mp + nqp) * C::kKGroups;
-    knn_tc_prep_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(z, zq, M, d, C::DP, C::NB, Mp, nq, nqp, bimg,
-                                                                           aimg, max_nrm_bits);
+    if (C::BF)
+        knn_tc_prep_bf16_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(z, zq, M, d, C::DP, C::NB, Mp, nq, nqp,
+                                                                                    bimg, aimg, max_nrm_bits);
+    else
+        knn_tc_prep_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(z, zq, M, d, C::DP, C::NB, Mp, nq, nqp, bimg,
+                                                                               aimg, max_nrm_bits);
     KERNEL_CHECK();
     const size_t smem = (size_t)C::ATILES * C::kTileBytes + (size_t)C::STAGES * C::kStageBytes +
                         (size_t)kL * C::kRowsPerCta * 8 + (size_t)C::kRowsPerCta * 4 + sizeof(TcBars<C::STAGES>) + 64;
@@ -482,6 +566,10 @@ int launch_tc(const float* z, const float* zq, int64_t M, int d, int64_t nq, flo
 }
 
 typedef Cfg<16, 2, 4, 1, 128, 1> Cfg16;    // N = 128 MMAs, two accumulator buffers per A tile, 8 epilogue warps
+typedef Cfg<16, 1, 3, 1, 128, 1, 1> Cfg16B;  // bf16 operands: 4 MMAs of K = 16 per tile and chunk instead of 7 of K = 8; 2 CTAs/SM
+typedef Cfg<16, 1, 2, 1, 64, 1, 1> Cfg16B64;  // the same with 64-candidate chunks: 128 TMEM columns, 3 CTAs/SM (experiment)
+typedef Cfg<32, 1, 2, 1, 128, 1, 1> Cfg32B;  // bf16: 7 MMAs instead of 13, one-tile CTA (95 KB): 2 CTAs/SM
+typedef Cfg<64, 2, 2, 1, 128, 1, 1> Cfg64B;  // bf16: 13 MMAs instead of 25, two 36 KB A tiles per CTA
 typedef Cfg<16, 1, 2, 1, 128, 1> Cfg16P;   // one A tile per CTA, TWO CTAs per SM: each CTA's MMAs fill the other's epilogue stalls
 typedef Cfg<16, 2, 4, 1, 128, 2> Cfg16E2;  // the same with 16 epilogue warps: two per 32-row block, 64 columns each
 typedef Cfg<16, 2, 3, 1, 256, 1> Cfg16W;   // N = 256 MMAs (half as many instructions), one buffer per A tile
@@ -496,14 +584,39 @@ static_assert(1 * Cfg64::kTileBytes + 3 * Cfg64::kStageBytes + kL * 128 * 8 < 22
 
 int knn_tc_dp(int d) { return d <= 16 ? 16 : d <= 32 ? 32 : 64; }
 int64_t knn_tc_padded_candidates(int64_t M) { return align_up(M, 256); }
-int64_t knn_tc_padded_queries(int64_t nq, int d) { return align_up(nq, d <= 32 ? 256 : 128); }
+int64_t knn_tc_padded_queries(int64_t nq, int d) {
+    (void)d;
+    return align_up(nq, 256);  // every configuration's CTA (128 or 256 query rows) divides it
+}
 int64_t knn_tc_image_floats(int64_t rows_padded, int d) { return rows_padded * (2 * knn_tc_dp(d) + 8); }
+
+// operand format of the filter: GEOCB_KNN_TC_FMT = bf16 | tf32
+static bool knn_tc_bf16() {
+    const char* e = getenv("GEOCB_KNN_TC_FMT");
+    return KNN_TC_DEFAULT_BF16 ? !(e && e[0] == 't') : (e && e[0] == 'b');
+}
+// bound on |filter score - exact score| / (|b|^2 + 2|a||b|), used by the certificate of the re-rank pass (knn.cu):
+//   tf32 hi+lo: dropped lo.lo term, tf32 truncation of lo, fp32 accumulation of <= 136 terms: 2^-17;
+//   bf16 hi+lo: x = hi + lo + r, |r| <= 2^-16|x| for both operands and the dropped lo.lo term: 3 * 2^-16 on the dot
+//   product, plus the fp32 accumulation and the 2^-24 norm split: 2^-14.
+double knn_tc_eps_unit(void) { return knn_tc_bf16() ? 6.103515625e-05 : 7.62939453125e-06; }
 
 int knn_filter_tc(const float* z, const float* zq, int64_t M, int d, int64_t nq, float* bimg, float* aimg,
                   unsigned int* max_nrm_bits, int32_t* cand_idx, float* cand_thr, cudaStream_t st) {
     if (d > 64) {
         geocb_set_error("knn_filter_tc supports d <= 64");
         return GEOCB_ERR_UNSUPPORTED;
+    }
+    if (knn_tc_bf16()) {
+        switch (knn_tc_dp(d)) {
+            case 16: {
+                const char* e = getenv("GEOCB_KNN_TC_N");
+                if (e && atoi(e) == 64) return launch_tc<Cfg16B64>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
+                return launch_tc<Cfg16B>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
+            }
+            case 32: return launch_tc<Cfg32B>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
+            default: return launch_tc<Cfg64B>(z, zq, M, d, nq, bimg, aimg, max_nrm_bits, cand_idx, cand_thr, st);
+        }
     }
     switch (knn_tc_dp(d)) {
         case 16: {

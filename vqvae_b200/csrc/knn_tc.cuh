@@ -3,11 +3,13 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-// d <= 64.  Candidates are padded to whole 128-row tiles, queries to whole CTAs (256 rows, 128 for d > 32).
+// d <= 64.  Candidates are padded to whole 256-row tiles, queries to 256 rows (every configuration's CTA divides it).
 int knn_tc_dp(int d);  // padded dimension of the operand images: 16, 32 or 64
 int64_t knn_tc_padded_candidates(int64_t M);
 int64_t knn_tc_padded_queries(int64_t nq, int d);
 int64_t knn_tc_image_floats(int64_t rows_padded, int d);  // floats of an operand image with that many rows
+// |filter score - exact score| <= knn_tc_eps_unit() * (|b|^2 + 2|a||b|) for the operand format in use (tf32 / bf16 split)
+double knn_tc_eps_unit(void);
 // filter pass: queries zq[nq][d] against candidates z[M][d]; writes cand_idx[nq][32] (candidate ids, -1 = empty,
 // ids >= M = pad rows) and cand_thr[nq] (every candidate not in the list has tensor-core score >= cand_thr).
 // bimg/aimg are scratch images.
