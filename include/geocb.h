@@ -110,6 +110,13 @@ int geocb_bn_relu_jvp(float* x, float* t, int64_t rows, int C, int HW, int rows_
 int geocb_bn_relu_jvp_to_image(const float* x, const float* t, int64_t rows, int C, int HW, int rows_per_group,
                                const float* pre_bias, const float* weight, const float* bias, float eps, int relu,
                                float* aimg, int64_t img_row_t, void* stream);
+/* geocb_lin_bn_relu_jvp_to_image: the linear map in FRONT of that BatchNorm fused in as well (the decoder's first
+ * layer on the 1x1 latent grid, riemannian_metric.py:12-35): zin / tin [rows][kin] are the primal / tangent latents,
+ * w_in [kin][C*HW] row-major the dense operator, kin = 16 or 32 (else GEOCB_ERR_UNSUPPORTED).  Pre-activations are kin
+ * sequential FMAs (k ascending) + pre_bias: the [rows][C*HW] matrix is never written or read. */
+int geocb_lin_bn_relu_jvp_to_image(const float* zin, const float* tin, int kin, const float* w_in, int64_t rows, int C,
+                                   int HW, int rows_per_group, const float* pre_bias, const float* weight,
+                                   const float* bias, float eps, int relu, float* aimg, int64_t img_row_t, void* stream);
 int geocb_gemm3x_supported(int64_t M, int K, int N);
 int geocb_gemm3x_prep_weights(const float* W, int K, int N, float* bimg, void* stream);
 int geocb_gemm3x(const float* A, int64_t M, int K, int N, const float* bimg, float* aimg, float* C, void* stream);

@@ -24,3 +24,31 @@ def test_gemm3x_matches_float64(M, K, N):
     print(f"M={M} K={K} N={N}: gemm3x err {err:.3g} (cuBLAS fp32 {cub:.3g}) of sum|a||w|")
     assert err < 2.5e-6  # measured 1.3-1.9e-6 (fp32 accumulation in the tensor core truncates); plain TF32 would be ~5e-4
     assert dg.gemm3x(a[:100], w) is None  # unsupported shape -> caller keeps the library GEMM
+
+
+@pytest.mark.parametrize("kin,C,HW", [(16, 128, 4), (32, 64, 8), (16, 512, 1)])
+def test_fused_input_layer_matches_unfused(kin, C, HW):
+    """geocb_lin_bn_relu_jvp_to_image (first linear map fused into the BatchNorm-JVP kernel) against the unfused pair
+    SGEMM + geocb_bn_relu_jvp_to_image: same operand image up to the SGEMM's summation order (1e-6 relative)."""
+    from vqvae_b200 import device_graph as dg
+    g = torch.Generator().manual_seed(kin + C)
+    n, groups, ld = 1024, 2, C * HW
+    z = torch.randn(n, kin, generator=g).cuda()
+    dz = (torch.randn(n, kin, generator=g) * 0.1).cuda()
+    w = (torch.randn(kin, ld, generator=g) / kin ** 0.5).cuda()
+    pb = torch.randn(ld, generator=g).cuda()
+    bw, bb = (torch.rand(C, generator=g) + 0.5).cuda(), torch.randn(C, generator=g).cuda()
+    img_a = torch.zeros(2 * 2 * n * ld, device="cuda")
+    img_b = torch.zeros_like(img_a)
+    assert dg.lin_bn_relu_jvp_to_image(z, dz, w, C, HW, n // groups, pb, bw, bb, 1e-5, True, (img_a, n))
+    torch.backends.cuda.matmul.allow_tf32 = False
+    x, t = (z @ w).contiguous(), (dz @ w).contiguous()
+    assert dg.bn_relu_jvp(x, t, C, HW, n // groups, pb, bw, bb, 1e-5, True, image=(img_b, n))
+    torch.cuda.synchronize()
+    a, b = img_a.cpu().numpy(), img_b.cpu().numpy()
+    # hi + lo of an element sit 2048 floats apart inside a (128-row, 16-column) tile pair; compare the recombined values
+    va = a.reshape(-1, 2, 2048).sum(axis=1)
+    vb = b.reshape(-1, 2, 2048).sum(axis=1)
+    scale = np.abs(vb).max()
+    assert np.abs(va - vb).max() <= 2e-6 * scale
+    assert (va != 0).mean() > 0.3  # (ReLU zeroes roughly half)

@@ -35,25 +35,56 @@ __device__ __forceinline__ void block_sum(float (&v)[NRED], float* s_red /* [8][
     }
 }
 
-// RPT rows per thread, CPB channels per slab (HW = 16 / CPB)
-template <int RPT, int CPB>
+// RPT rows per thread, CPB channels per slab (HW = 16 / CPB).
+// KIN > 0: the linear map in front of this BatchNorm is fused in -- x / t are then its INPUT rows [rows][KIN] (primal
+// and tangent latents) and w_in [KIN][ld] its matrix: the slab's pre-activations are KIN sequential FMAs per value (k
+// ascending, the order of a SIMT SGEMM), so the [rows][ld] pre-activation matrix is never written or read.
+template <int RPT, int CPB, int KIN>
 __global__ void __launch_bounds__(kBnThreads) bn_relu_jvp_kernel(float* __restrict__ x, float* __restrict__ t, int R,
                                                                  int ld, const float* __restrict__ pre_bias,
                                                                  const float* __restrict__ weight,
                                                                  const float* __restrict__ bias, float eps, int relu,
-                                                                 float* __restrict__ img, int64_t img_row_t) {
+                                                                 float* __restrict__ img, int64_t img_row_t,
+                                                                 const float* __restrict__ w_in) {
     constexpr int HW = 16 / CPB;
     __shared__ float s_red[(kBnThreads / 32) * 2 * CPB];
+    __shared__ float s_w[(KIN > 0 ? KIN : 1) * 16];
     const int col0 = blockIdx.x * 16;
     const int64_t row0 = (int64_t)blockIdx.y * R;
     float xv[RPT][16], tv[RPT][16];
     float pb[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) pb[i] = pre_bias ? pre_bias[col0 + i] : 0.f;
+    if (KIN > 0) {
+        for (int i = threadIdx.x; i < KIN * 16; i += kBnThreads) s_w[i] = w_in[(int64_t)(i >> 4) * ld + col0 + (i & 15)];
+        __syncthreads();
+    }
 #pragma unroll
     for (int k = 0; k < RPT; ++k) {
         const int r = threadIdx.x + k * kBnThreads;
-        if (r < R) {
+        if (KIN > 0) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) xv[k][i] = 0.f, tv[k][i] = 0.f;
+            if (r < R) {
+                const float4* pz = (const float4*)(x + (row0 + r) * KIN);
+                const float4* pd = (const float4*)(t + (row0 + r) * KIN);
+#pragma unroll
+                for (int j4 = 0; j4 < KIN / 4; ++j4) {
+                    const float4 a = pz[j4], b = pd[j4];
+                    const float za[4] = {a.x, a.y, a.z, a.w}, zb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const float w = s_w[(4 * j4 + jj) * 16 + i];
+                            xv[k][i] = __fmaf_rn(za[jj], w, xv[k][i]);
+                            tv[k][i] = __fmaf_rn(zb[jj], w, tv[k][i]);
+                        }
+                }
+#pragma unroll
+                for (int i = 0; i < 16; ++i) xv[k][i] += pb[i];
+            }
+        } else if (r < R) {
             const float4* px = (const float4*)(x + (row0 + r) * ld + col0);
             const float4* pt = (const float4*)(t + (row0 + r) * ld + col0);
 #pragma unroll
@@ -183,15 +214,16 @@ __global__ void __launch_bounds__(kBnThreads) bn_relu_jvp_kernel(float* __restri
     }
 }
 
-template <int RPT>
+template <int RPT, int KIN>
 int launch_bn(int cpb, dim3 grid, cudaStream_t st, float* x, float* t, int R, int ld, const float* pre_bias,
-              const float* weight, const float* bias, float eps, int relu, float* img, int64_t img_row_t) {
+              const float* weight, const float* bias, float eps, int relu, float* img, int64_t img_row_t,
+              const float* w_in) {
     switch (cpb) {
-        case 1: bn_relu_jvp_kernel<RPT, 1><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t); break;
-        case 2: bn_relu_jvp_kernel<RPT, 2><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t); break;
-        case 4: bn_relu_jvp_kernel<RPT, 4><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t); break;
-        case 8: bn_relu_jvp_kernel<RPT, 8><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t); break;
-        case 16: bn_relu_jvp_kernel<RPT, 16><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t); break;
+        case 1: bn_relu_jvp_kernel<RPT, 1, KIN><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t, w_in); break;
+        case 2: bn_relu_jvp_kernel<RPT, 2, KIN><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t, w_in); break;
+        case 4: bn_relu_jvp_kernel<RPT, 4, KIN><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t, w_in); break;
+        case 8: bn_relu_jvp_kernel<RPT, 8, KIN><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t, w_in); break;
+        case 16: bn_relu_jvp_kernel<RPT, 16, KIN><<<grid, kBnThreads, 0, st>>>(x, t, R, ld, pre_bias, weight, bias, eps, relu, img, img_row_t, w_in); break;
         default: return GEOCB_ERR_UNSUPPORTED;
     }
     KERNEL_CHECK();
@@ -200,7 +232,8 @@ int launch_bn(int cpb, dim3 grid, cudaStream_t st, float* x, float* t, int R, in
 }  // namespace
 
 static int bn_impl(float* x, float* t, int64_t rows, int C, int HW, int rows_per_group, const float* pre_bias,
-                   const float* weight, const float* bias, float eps, int relu, float* img, int64_t img_row_t, void* stream) {
+                   const float* weight, const float* bias, float eps, int relu, float* img, int64_t img_row_t, void* stream,
+                   const float* w_in = nullptr, int kin = 0) {
     ARG_CHECK(x && t && rows > 0 && C > 0 && HW > 0 && rows_per_group > 0);
     if (!(HW == 1 || HW == 2 || HW == 4 || HW == 8 || HW == 16) || (C * HW) % 16 != 0 || rows % rows_per_group != 0 ||
         rows_per_group > 2 * kBnThreads || rows / rows_per_group > 65535) {
@@ -211,9 +244,16 @@ static int bn_impl(float* x, float* t, int64_t rows, int C, int HW, int rows_per
     const dim3 grid((unsigned)(C * HW / 16), (unsigned)(rows / rows_per_group));
     cudaStream_t st = (cudaStream_t)stream;
     const int cpb = 16 / HW, ld = C * HW;
-    if (rows_per_group <= kBnThreads)
-        return launch_bn<1>(cpb, grid, st, x, t, rows_per_group, ld, pre_bias, weight, bias, eps, relu, img, img_row_t);
-    return launch_bn<2>(cpb, grid, st, x, t, rows_per_group, ld, pre_bias, weight, bias, eps, relu, img, img_row_t);
+    const bool one = rows_per_group <= kBnThreads;
+#define BN_LAUNCH(KIN)                                                                                                     \
+    (one ? launch_bn<1, KIN>(cpb, grid, st, x, t, rows_per_group, ld, pre_bias, weight, bias, eps, relu, img, img_row_t, w_in) \
+         : launch_bn<2, KIN>(cpb, grid, st, x, t, rows_per_group, ld, pre_bias, weight, bias, eps, relu, img, img_row_t, w_in))
+    if (kin == 0) return BN_LAUNCH(0);
+    if (kin == 16) return BN_LAUNCH(16);
+    if (kin == 32) return BN_LAUNCH(32);
+#undef BN_LAUNCH
+    geocb_set_error("lin_bn_relu_jvp: fused input width %d not supported (16 or 32)", kin);
+    return GEOCB_ERR_UNSUPPORTED;
 }
 
 GEOCB_API int geocb_bn_relu_jvp(float* x, float* t, int64_t rows, int C, int HW, int rows_per_group,
@@ -228,4 +268,15 @@ GEOCB_API int geocb_bn_relu_jvp_to_image(const float* x, const float* t, int64_t
     ARG_CHECK(aimg && img_row_t >= rows && rows % 128 == 0 && img_row_t % 128 == 0);
     return bn_impl((float*)x, (float*)t, rows, C, HW, rows_per_group, pre_bias, weight, bias, eps, relu, aimg, img_row_t,
                    stream);
+}
+
+// The linear map in front of the BatchNorm fused in (kin = 16 or 32 input features, e.g. the latent dimension):
+// zin / tin [rows][kin] primal and tangent inputs, w_in [kin][C*HW] row-major; writes the next GEMM's operand image.
+GEOCB_API int geocb_lin_bn_relu_jvp_to_image(const float* zin, const float* tin, int kin, const float* w_in, int64_t rows,
+                                             int C, int HW, int rows_per_group, const float* pre_bias, const float* weight,
+                                             const float* bias, float eps, int relu, float* aimg, int64_t img_row_t,
+                                             void* stream) {
+    ARG_CHECK(zin && tin && w_in && aimg && img_row_t >= rows && rows % 128 == 0 && img_row_t % 128 == 0);
+    return bn_impl((float*)zin, (float*)tin, rows, C, HW, rows_per_group, pre_bias, weight, bias, eps, relu, aimg,
+                   img_row_t, stream, w_in, kin);
 }

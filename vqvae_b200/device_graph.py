@@ -279,6 +279,23 @@ def bn_relu_jvp(x, t, C_, HW, rows_per_group, pre_bias, weight, bias, eps, relu,
     return True
 
 
+def lin_bn_relu_jvp_to_image(z, dz, w, C_, HW, rows_per_group, pre_bias, weight, bias, eps, relu, image):
+    """z @ w (+pre_bias) -> BatchNorm(train) JVP (+ReLU) -> operand image of the next tcgen05 GEMM, in one kernel
+    (geocb_lin_bn_relu_jvp_to_image).  z / dz [rows, kin] primal / tangent inputs, w [kin, C*HW].  Returns False when
+    the shape is outside what the kernel supports."""
+    lib = _lib.load()
+    rows, kin = z.shape
+    if not (kin in (16, 32) and HW in (1, 2, 4, 8, 16) and (C_ * HW) % 16 == 0 and rows % rows_per_group == 0
+            and rows_per_group <= 512 and rows // rows_per_group <= 65535 and rows % 128 == 0 and z.is_contiguous()
+            and dz.is_contiguous() and w.is_contiguous() and tuple(w.shape) == (kin, C_ * HW)):
+        return False
+    aimg, row_t = image
+    check(lib.geocb_lin_bn_relu_jvp_to_image(ptr(z), ptr(dz), kin, ptr(w), rows, C_, HW, rows_per_group, ptr(pre_bias),
+                                             ptr(weight), ptr(bias), float(eps), int(relu), ptr(aimg), int(row_t),
+                                             stream_ptr()), "lin_bn_relu_jvp_to_image")
+    return True
+
+
 _gemm3x_weights = {}
 
 

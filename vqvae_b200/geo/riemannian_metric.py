@@ -314,6 +314,21 @@ def _forward_mode(ops, z, dz, groups):
         op = ops[i]
         if op[0] == "lin":
             fusable = _bn_fusable(ops, i + 1, n, groups)
+            if i == 0 and fusable and op[1].shape[0] in (16, 32) and os.environ.get("GEOCB_JVP_FUSE_IN", "1") != "0":
+                # first layer (latent -> first feature map) + BatchNorm + ReLU + operand image of the wide GEMM behind
+                # them in ONE kernel: the pre-activation matrix is never materialised
+                m, shape = ops[1][1], ops[1][2]
+                relu_next = len(ops) > 2 and ops[2][0] == "relu"
+                j = 3 if relu_next else 2
+                if (j < len(ops) and ops[j][0] == "lin" and _wants_tc(ops[j][1], _bn_fusable(ops, j + 1, n, groups))
+                        and n % 128 == 0 and ops[j][1].shape[0] == shape[0] * shape[1] * shape[2]
+                        and dg.gemm3x_supported(2 * n, ops[j][1].shape[0], ops[j][1].shape[1])):
+                    image = (dg.gemm3x_image_buffer(2 * n, ops[j][1].shape[0], x.device), n)
+                    if dg.lin_bn_relu_jvp_to_image(x.contiguous(), t.contiguous(), op[1], shape[0], shape[1] * shape[2],
+                                                   n // groups, op[2], m.weight, m.bias, m.eps, relu_next, image):
+                        in_image = True
+                        i = j
+                        continue
             if in_image:
                 y = dg.gemm3x(None, op[1], M=2 * n)
                 in_image = False

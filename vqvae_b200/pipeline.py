@@ -87,20 +87,23 @@ def build_codebook_device(z4: torch.Tensor, decoder, k=20, sym="union", K=512, i
     side = torch.cuda.Stream(device=dev)
 
     def overlap_decoder_setup():
-        # the kNN kernel is in flight (nothing above synchronises): edge-length set-up could run in its shadow.
-        # Measured on B200 and rejected, so OFF unless asked for (GEOCB_OVERLAP_DECODER_SETUP):
-        #   "1"    = run the decoder once on a side stream: saves 0.15 s of set-up, slows the one-CTA-per-SM kNN filter
-        #            by 0.3-0.5 s (tools/gpu_r2_run15.sh);
-        #   "host" = host-only part (unroll the decoder on the CPU, upload the operators through the copy engine, create
-        #            the GEMM library handle): edge_len 2.33 -> 2.27 s, kNN 2.29 -> 2.37-2.41 s, total unchanged
-        #            (tools/gpu_r2_quick.sh).
+        # the kNN kernel is in flight (nothing above synchronises): host-side edge-length set-up runs in its shadow.
+        # GEOCB_OVERLAP_DECODER_SETUP, measured on B200:
+        #   "blas" (default) = create the GEMM library handle only (~0.1 s of host work, no kernels, no copies):
+        #            edge_len 2.16-2.26 -> 2.12-2.13 s, kNN unchanged (tools/gpu_r2_edge2.sh);
+        #   "host" = also unroll the decoder on the CPU and upload the operators through the copy engine: edge_len
+        #            2.33 -> 2.27 s but kNN 2.29 -> 2.37-2.41 s (tools/gpu_r2_quick.sh): rejected;
+        #   "1"    = run the decoder once on a side stream: saves 0.15 s of set-up, slows the kNN filter by 0.3-0.5 s
+        #            (tools/gpu_r2_run15.sh): rejected;   "0" = nothing.
         import os
-        mode = os.environ.get("GEOCB_OVERLAP_DECODER_SETUP", "0")
+        mode = os.environ.get("GEOCB_OVERLAP_DECODER_SETUP", "blas")
         if mode == "0":
             return
         with torch.cuda.stream(side):
             if mode == "1":
                 warm_up_decoder(decoder, C, batch_size)
+            elif mode == "blas":  # only the GEMM library handle (~0.1 s of host work, no kernels, no copies)
+                torch.cuda.current_blas_handle()
             else:
                 decoder_plan(decoder, C)
                 torch.cuda.current_blas_handle()
