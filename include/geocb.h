@@ -117,6 +117,12 @@ int geocb_bn_relu_jvp_to_image(const float* x, const float* t, int64_t rows, int
 int geocb_lin_bn_relu_jvp_to_image(const float* zin, const float* tin, int kin, const float* w_in, int64_t rows, int C,
                                    int HW, int rows_per_group, const float* pre_bias, const float* weight,
                                    const float* bias, float eps, int relu, float* aimg, int64_t img_row_t, void* stream);
+/* geocb_lin_sigmoid_jvp: the decoder's LAST linear map fused with the sigmoid and its tangent
+ * (riemannian_metric.py:29-35): out[r][p] = s (1 - s) (t[r,:] . w[:,p]), s = sigmoid(x[r,:] . w[:,p] + bias[p]).
+ * x / t [rows][K] primal / tangent activations, w [K][P] row-major, bias [P] or NULL, out [rows][P].
+ * P = 16 and K a multiple of 128 (else GEOCB_ERR_UNSUPPORTED: the caller keeps the library GEMM). */
+int geocb_lin_sigmoid_jvp(const float* x, const float* t, int64_t rows, int K, int P, const float* w, const float* bias,
+                          float* out, void* stream);
 int geocb_gemm3x_supported(int64_t M, int K, int N);
 int geocb_gemm3x_prep_weights(const float* W, int K, int N, float* bimg, void* stream);
 int geocb_gemm3x(const float* A, int64_t M, int K, int N, const float* bimg, float* aimg, float* C, void* stream);

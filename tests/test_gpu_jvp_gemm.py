@@ -52,3 +52,27 @@ def test_fused_input_layer_matches_unfused(kin, C, HW):
     scale = np.abs(vb).max()
     assert np.abs(va - vb).max() <= 2e-6 * scale
     assert (va != 0).mean() > 0.3  # (ReLU zeroes roughly half)
+
+
+@pytest.mark.parametrize("rows,K", [(128, 128), (1000, 1024), (65536, 1024)])
+def test_last_layer_sigmoid_jvp(rows, K):
+    """geocb_lin_sigmoid_jvp against float64: s (1 - s) (t @ w), s = sigmoid(x @ w + b)."""
+    from vqvae_b200 import device_graph as dg
+    g = torch.Generator().manual_seed(rows + K)
+    x = torch.relu(torch.randn(rows, K, generator=g)).cuda()
+    t = (torch.randn(rows, K, generator=g) * 0.1).cuda()
+    w = (torch.randn(K, 16, generator=g) * 0.05).cuda()
+    b = torch.randn(16, generator=g).cuda()
+    out = dg.lin_sigmoid_jvp(x, t, w, b)
+    assert out is not None and out.shape == (rows, 16)
+    y64 = x.double() @ w.double() + b.double()
+    s64 = torch.sigmoid(y64)
+    ref = s64 * (1 - s64) * (t.double() @ w.double())
+    scale = (t.double().abs() @ w.double().abs()).clamp_min(1e-30) * 0.25
+    err = ((out.double() - ref).abs() / scale).max().item()
+    lib = torch.sigmoid(x @ w + b)
+    lib = (lib * (1 - lib) * (t @ w)).double()
+    err_lib = ((lib - ref).abs() / scale).max().item()
+    print(f"rows={rows} K={K}: fused {err:.3g}, library ops {err_lib:.3g} (of 0.25 sum|t||w|)")
+    assert err < 2e-6
+    assert dg.lin_sigmoid_jvp(x, t, w[:, :8].contiguous(), None) is None  # unsupported width -> library path

@@ -35,6 +35,7 @@ SIGNATURES = {
     "geocb_bn_relu_jvp": (_int, [_p, _p, _i64, _int, _int, _int, _p, _p, _p, C.c_float, _int, _p]),
     "geocb_bn_relu_jvp_to_image": (_int, [_p, _p, _i64, _int, _int, _int, _p, _p, _p, C.c_float, _int, _p, _i64, _p]),
     "geocb_lin_bn_relu_jvp_to_image": (_int, [_p, _p, _int, _p, _i64, _int, _int, _int, _p, _p, _p, C.c_float, _int, _p, _i64, _p]),
+    "geocb_lin_sigmoid_jvp": (_int, [_p, _p, _i64, _int, _int, _p, _p, _p, _p]),
     "geocb_gemm3x_supported": (_int, [_i64, _int, _int]),
     "geocb_gemm3x_prep_weights": (_int, [_p, _int, _int, _p, _p]),
     "geocb_gemm3x": (_int, [_p, _i64, _int, _int, _p, _p, _p, _p]),

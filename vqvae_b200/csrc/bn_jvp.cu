@@ -280,3 +280,92 @@ GEOCB_API int geocb_lin_bn_relu_jvp_to_image(const float* zin, const float* tin,
     return bn_impl((float*)zin, (float*)tin, rows, C, HW, rows_per_group, pre_bias, weight, bias, eps, relu, aimg,
                    img_row_t, stream, w_in, kin);
 }
+
+// ---------------------------------------------------------------- last layer ----
+// out[r][p] = s (1 - s) (t[r,:] . W[:,p]),  s = sigmoid(x[r,:] . W[:,p] + b[p])      (riemannian_metric.py:29-35: the
+// tangent of sigmoid(decoder(z)) through the decoder's last linear map) for a narrow output (P = 16: the 4x4 patch a
+// 1x1 latent cell decodes to).  A [rows x K] x [K x 16] product is memory-bound (it reads x and t once: 16 FMAs per
+// loaded float); the library's SIMT SGEMM needs 195 us for 131 072 x 1024 x 16 where the reads take 82 us, and it is
+// the only library GEMM left on the path (the handle alone costs 0.1 s per process).
+namespace {
+constexpr int kFinP = 16, kFinRows = 64, kFinKC = 128, kFinThreads = 256, kFinLd = kFinKC + 4;
+
+// CTA = 64 rows, 256 threads: thread = 4 rows x 1 output column, operands staged through shared memory in K-chunks of
+// 128, W transposed there so that both operands are read 16 bytes at a time; four partial sums per value (k mod 4),
+// combined pairwise.  223 us for 65 536 x 1024 rows of x and t, the same as the library SGEMM + its three elementwise
+// kernels; other tilings measured slower (4 x 2 outputs per thread, 39 KB CTAs: 291 us; a quad of lanes per row with
+// all 16 outputs in registers and W whole in shared memory: 506 us) - the shared-memory reads bound all of them.
+__global__ void __launch_bounds__(kFinThreads) lin_sigmoid_jvp_kernel(const float* __restrict__ x, const float* __restrict__ t,
+                                                                       int64_t rows, int K, const float* __restrict__ w,
+                                                                       const float* __restrict__ bias,
+                                                                       float* __restrict__ out) {
+    extern __shared__ __align__(16) float s_fin[];
+    float* xs = s_fin;                       // [64][132]
+    float* ts = xs + kFinRows * kFinLd;      // [64][132]
+    float* wt = ts + kFinRows * kFinLd;      // [16][132]
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const int64_t row0 = (int64_t)blockIdx.x * kFinRows;
+    float4 ax[4], at[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) ax[i] = at[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int k0 = 0; k0 < K; k0 += kFinKC) {
+        __syncthreads();  // the previous chunk has been consumed
+#pragma unroll
+        for (int j = 0; j < (kFinRows * kFinKC / 4) / kFinThreads; ++j) {
+            const int idx = threadIdx.x + j * kFinThreads;
+            const int r = idx >> 5, c4 = idx & 31;
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+            if (row0 + r < rows) {
+                a = *(const float4*)(x + (row0 + r) * K + k0 + 4 * c4);
+                b = *(const float4*)(t + (row0 + r) * K + k0 + 4 * c4);
+            }
+            *(float4*)(xs + r * kFinLd + 4 * c4) = a;
+            *(float4*)(ts + r * kFinLd + 4 * c4) = b;
+        }
+#pragma unroll
+        for (int j = 0; j < (kFinKC * kFinP) / kFinThreads; ++j) {
+            const int idx = threadIdx.x + j * kFinThreads;  // = k * 16 + p
+            wt[(idx & 15) * kFinLd + (idx >> 4)] = w[(int64_t)k0 * kFinP + idx];
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int k4 = 0; k4 < kFinKC / 4; ++k4) {
+            const float4 wv = *(const float4*)(wt + tx * kFinLd + 4 * k4);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float4 a = *(const float4*)(xs + (4 * ty + i) * kFinLd + 4 * k4);
+                const float4 b = *(const float4*)(ts + (4 * ty + i) * kFinLd + 4 * k4);
+                ax[i].x = __fmaf_rn(a.x, wv.x, ax[i].x), ax[i].y = __fmaf_rn(a.y, wv.y, ax[i].y);
+                ax[i].z = __fmaf_rn(a.z, wv.z, ax[i].z), ax[i].w = __fmaf_rn(a.w, wv.w, ax[i].w);
+                at[i].x = __fmaf_rn(b.x, wv.x, at[i].x), at[i].y = __fmaf_rn(b.y, wv.y, at[i].y);
+                at[i].z = __fmaf_rn(b.z, wv.z, at[i].z), at[i].w = __fmaf_rn(b.w, wv.w, at[i].w);
+            }
+        }
+    }
+    const float bp = bias ? bias[tx] : 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int64_t r = row0 + 4 * ty + i;
+        if (r >= rows) continue;
+        const float y = ((ax[i].x + ax[i].y) + (ax[i].z + ax[i].w)) + bp;
+        const float tt = (at[i].x + at[i].y) + (at[i].z + at[i].w);
+        const float s = 1.0f / (1.0f + expf(-y));
+        out[r * kFinP + tx] = (s * (1.0f - s)) * tt;
+    }
+}
+}  // namespace
+
+GEOCB_API int geocb_lin_sigmoid_jvp(const float* x, const float* t, int64_t rows, int K, int P, const float* w,
+                                    const float* bias, float* out, void* stream) {
+    ARG_CHECK(x && t && w && out && rows > 0 && K > 0);
+    if (P != kFinP || K % kFinKC != 0) {
+        geocb_set_error("lin_sigmoid_jvp: P = %d, K = %d not supported (P = 16, K a multiple of 128)", P, K);
+        return GEOCB_ERR_UNSUPPORTED;
+    }
+    const size_t smem = (size_t)(2 * kFinRows + kFinP) * kFinLd * sizeof(float);
+    CU_TRY(cudaFuncSetAttribute(lin_sigmoid_jvp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    lin_sigmoid_jvp_kernel<<<(unsigned)((rows + kFinRows - 1) / kFinRows), kFinThreads, smem, (cudaStream_t)stream>>>(
+        x, t, rows, K, w, bias, out);
+    KERNEL_CHECK();
+    return 0;
+}

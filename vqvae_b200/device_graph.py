@@ -296,6 +296,19 @@ def lin_bn_relu_jvp_to_image(z, dz, w, C_, HW, rows_per_group, pre_bias, weight,
     return True
 
 
+def lin_sigmoid_jvp(x, t, w, bias):
+    """s (1 - s) (t @ w) with s = sigmoid(x @ w + bias) in one kernel (geocb_lin_sigmoid_jvp); None when the shape is
+    outside what the kernel supports (P = 16 outputs, K a multiple of 128)."""
+    K, P = w.shape
+    if not (P == 16 and K % 128 == 0 and x.is_contiguous() and t.is_contiguous() and w.is_contiguous()
+            and x.shape == t.shape and x.shape[1] == K and x.dtype == torch.float32):
+        return None
+    out = torch.empty((x.shape[0], P), dtype=torch.float32, device=x.device)
+    check(_lib.load().geocb_lin_sigmoid_jvp(ptr(x), ptr(t), x.shape[0], K, P, ptr(w), ptr(bias), ptr(out), stream_ptr()),
+          "lin_sigmoid_jvp")
+    return out
+
+
 _gemm3x_weights = {}
 
 

@@ -329,6 +329,13 @@ def _forward_mode(ops, z, dz, groups):
                         in_image = True
                         i = j
                         continue
+            if (i == len(ops) - 1 and not in_image and os.environ.get("GEOCB_JVP_FUSE_OUT", "1") != "0"
+                    and x.shape == t.shape):
+                # last layer + sigmoid + its tangent in one kernel (narrow outputs: the library SGEMM is 2.4x off the
+                # memory time there, and it would be the only library GEMM left on the path)
+                j = dg.lin_sigmoid_jvp(x.contiguous(), t.contiguous(), op[1], op[2])
+                if j is not None:
+                    return j
             if in_image:
                 y = dg.gemm3x(None, op[1], M=2 * n)
                 in_image = False
@@ -380,6 +387,33 @@ def _forward_mode(ops, z, dz, groups):
         i += 1
     s = torch.sigmoid(x)  # always applied (:29)
     return s * (1 - s) * t
+
+
+def decoder_needs_library_gemm(decoder, latent_dim) -> bool:
+    """Cheap structural guess (shapes only, no tensor work): will the edge-length stage call a library GEMM for this
+    decoder?  It does not when the first layer fuses into the BatchNorm kernel (latent_dim 16 / 32), the middle layers
+    run on the tcgen05 GEMM and the output patch of a latent cell has 16 values (geocb_lin_sigmoid_jvp).  Used by the
+    pipeline to decide whether creating the library handle in the kNN kernel's shadow is worth 0.1 s of host time."""
+    if _is_flat_decoder(decoder):
+        return True
+    layers = _flatten_layers(decoder)
+    if layers is None or latent_dim not in (16, 32):
+        return True
+    shape = (latent_dim, 1, 1)
+    for m in layers:
+        if isinstance(m, (nn.Conv2d, nn.ConvTranspose2d)):
+            if m.groups != 1 or isinstance(m.padding, str):
+                return True
+            (sh, sw), (ph, pw), (dh, dw) = m.stride, m.padding, m.dilation
+            kh, kw = m.kernel_size
+            if isinstance(m, nn.ConvTranspose2d):
+                oph, opw = m.output_padding
+                shape = (m.out_channels, (shape[1] - 1) * sh - 2 * ph + dh * (kh - 1) + oph + 1,
+                         (shape[2] - 1) * sw - 2 * pw + dw * (kw - 1) + opw + 1)
+            else:
+                shape = (m.out_channels, (shape[1] + 2 * ph - dh * (kh - 1) - 1) // sh + 1,
+                         (shape[2] + 2 * pw - dw * (kw - 1) - 1) // sw + 1)
+    return shape[0] * shape[1] * shape[2] != 16
 
 
 def decoder_plan(decoder, latent_dim):

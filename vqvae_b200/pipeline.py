@@ -19,7 +19,7 @@ from . import _lib
 from . import device_graph as dg
 from .sharding import shard_range, all_gather_rows  # noqa: F401  (re-exported)
 from .geo.knn_graph_optimized import knn_graph_device
-from .geo.riemannian_metric import decoder_plan, edge_lengths_device, warm_up_decoder
+from .geo.riemannian_metric import decoder_needs_library_gemm, decoder_plan, edge_lengths_device, warm_up_decoder
 from .geo.kmeans_optimized import fit_kmedoids_optimized
 
 
@@ -89,14 +89,18 @@ def build_codebook_device(z4: torch.Tensor, decoder, k=20, sym="union", K=512, i
     def overlap_decoder_setup():
         # the kNN kernel is in flight (nothing above synchronises): host-side edge-length set-up runs in its shadow.
         # GEOCB_OVERLAP_DECODER_SETUP, measured on B200:
-        #   "blas" (default) = create the GEMM library handle only (~0.1 s of host work, no kernels, no copies):
-        #            edge_len 2.16-2.26 -> 2.12-2.13 s, kNN unchanged (tools/gpu_r2_edge2.sh);
+        #   "blas" = create the GEMM library handle only (~0.1 s of host work, no kernels, no copies):
+        #            edge_len 2.16-2.26 -> 2.12-2.13 s, kNN unchanged (tools/gpu_r2_edge2.sh).  This is what the default
+        #            "auto" does when the decoder will call a library GEMM at all (decoder_needs_library_gemm: the
+        #            reference's FashionMNIST decoder does not - every layer has its own kernel);
         #   "host" = also unroll the decoder on the CPU and upload the operators through the copy engine: edge_len
         #            2.33 -> 2.27 s but kNN 2.29 -> 2.37-2.41 s (tools/gpu_r2_quick.sh): rejected;
         #   "1"    = run the decoder once on a side stream: saves 0.15 s of set-up, slows the kNN filter by 0.3-0.5 s
         #            (tools/gpu_r2_run15.sh): rejected;   "0" = nothing.
         import os
-        mode = os.environ.get("GEOCB_OVERLAP_DECODER_SETUP", "blas")
+        mode = os.environ.get("GEOCB_OVERLAP_DECODER_SETUP", "auto")
+        if mode == "auto":
+            mode = "blas" if decoder_needs_library_gemm(decoder, C) else "0"
         if mode == "0":
             return
         with torch.cuda.stream(side):
