@@ -62,7 +62,20 @@ def dijkstra_multi_source(W: sparse.spmatrix, sources, directed: bool = False, u
     """Multi-source geodesic distances (:24-50): (S,n) array, inf where unreachable."""
     if len(sources) == 0:
         raise ValueError("sources must be a non-empty sequence of node indices")  # :26-27
+    import os
+    trace = os.environ.get("GEOCB_TRACE_E2E") == "1"  # per-stage wall clock on stderr (diagnostics; adds synchronisation)
+    if trace:
+        import sys
+        import time
+        torch.cuda.synchronize()
+        _t = [time.perf_counter()]
+
+        def _mark():
+            torch.cuda.synchronize()
+            _t.append(time.perf_counter())
     g = graph_to_device(W, directed)
+    if trace:
+        _mark()
     src = np.asarray(sources, dtype=int)
     if g.n == 0:
         raise ValueError("empty graph")
@@ -78,13 +91,23 @@ def dijkstra_multi_source(W: sparse.spmatrix, sources, directed: bool = False, u
         return D
     # device->host copies of one batch of sources overlap the next batch's kernel (dg.sssp_multi_to_host); the result
     # lands in pinned memory (torch's caching host allocator recycles the block once the caller drops the array)
+    if trace:
+        g.adjacency(use_unit)
+        _mark()
     big = len(src) * g.n * 4 >= (8 << 20)
     D = torch.empty((len(src), g.n), dtype=torch.float32, pin_memory=big)
+    if trace:
+        _mark()
     P = torch.empty((len(src), g.n), dtype=torch.int32, pin_memory=big) if return_predecessors else None
     g_in = None
     if return_predecessors and directed and not isinstance(W, dg.DeviceCSR):
         g_in = dg.DeviceCSR.from_scipy(W.T.tocsr(), g.indptr.device)  # predecessors are searched over in-edges
     dg.sssp_multi_to_host(g, src, D, unweighted=use_unit, pred_host=P, g_in=g_in)
+    if trace:
+        _mark()
+        d = [1e3 * (b - a) for a, b in zip(_t[:-1], _t[1:])]
+        print(f"[e2e trace] graph_to_device {d[0]:.1f} ms  adjacency {d[1]:.1f}  result alloc {d[2]:.1f}  "
+              f"sssp_multi_to_host {d[3]:.1f}", file=sys.stderr, flush=True)
     if return_predecessors:
         return D.numpy().astype(dtype, copy=False), P.numpy()  # :42
     return D.numpy().astype(dtype, copy=False)  # :50
