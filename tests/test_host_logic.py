@@ -83,6 +83,24 @@ def test_unrolled_decoder_matches_module_forward():
     assert torch.allclose(x, want, rtol=1e-5, atol=1e-6)
 
 
+def test_decoder_needs_library_gemm_guess():
+    """The structural guess behind the pipeline's set-up overlap agrees with the unrolled operators: the reference's
+    FashionMNIST decoder (latent 16 -> 4x4 patch = 16 outputs) runs on this repo's kernels only, the CIFAR one
+    (3 x 8 x 8 = 192 outputs) and a flat decoder still call a library GEMM."""
+    import torch.nn as nn
+    from conftest import CIFAR_CFG, FASHION_CFG
+    from vqvae_b200.geo import riemannian_metric as rm
+    from vqvae_b200.models import SpatialVAE
+    for cfg, expect in ((FASHION_CFG, False), (CIFAR_CFG, True)):
+        dec = SpatialVAE(**cfg).decoder
+        assert rm.decoder_needs_library_gemm(dec, cfg["latent_dim"]) is expect
+        ops = rm._unrolled_ops(rm._flatten_layers(dec), cfg["latent_dim"])
+        width = [o for o in ops if o[0] == "lin"][-1][1].shape[1]
+        assert (width != 16) is expect
+    assert rm.decoder_needs_library_gemm(SpatialVAE(**FASHION_CFG).decoder, 24) is True   # first layer not fusable
+    assert rm.decoder_needs_library_gemm(nn.Sequential(nn.Linear(16, 8)), 16) is True     # not a conv stack
+
+
 def test_shard_ranges_keep_whole_bn_batches():
     from vqvae_b200.pipeline import shard_range
     E, bs = 46_400_123, 512
